@@ -1,0 +1,126 @@
+/* tts_b200.h -- C ABI of the B200-native TransformerTTS hot path.
+ *
+ * The reference (Orca0917/TransformerTTS) has no FFI layer: its boundary for this path is the Python
+ * class model.TransformerTTS (model/model.py:138-394).  This header is what a binding of that class
+ * calls: plain pointers and sizes, no C++ or torch types.  All data pointers are DEVICE pointers owned
+ * by the caller (PyTorch in the shipped host code); the library never allocates or frees device memory,
+ * launches asynchronously on the given stream (a cudaStream_t passed as void*), and is re-entrant across
+ * distinct weight/workspace sets (one per GPU).  Every entry point returns 0 on success or a non-zero
+ * status with a message available from tts_last_error() (thread-local).
+ *
+ * Reference interface replaced by each entry point:
+ *   tts_forward          TransformerTTS.forward                model/model.py:260-320
+ *   tts_encode           encoder half of TransformerTTS.inference   model/model.py:342-348
+ *   tts_decode           AR loop of TransformerTTS.inference    model/model.py:351-384
+ *   tts_postnet          PostNet + residual                     model/model.py:129-135, 310, 388
+ *   tts_op_linear / tts_op_conv1d / tts_op_attention
+ *                        the torch.nn operators underneath (model/module.py:4-53,
+ *                        torch/nn/functional.py:5798,6620-6665), exported for per-operator parity tests
+ */
+#ifndef TTS_B200_H
+#define TTS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TTS_ABI_VERSION 1
+
+/* flags */
+#define TTS_FLAG_WANT_ALIGN 1 /* tts_forward: store cross-attention probabilities into `align` */
+#define TTS_FLAG_ENC_MASK 2   /* apply the phoneme key-padding mask in the encoder (forward: yes, inference: no) */
+
+/* activation codes for the operator-level entry points */
+#define TTS_ACT_NONE 0
+#define TTS_ACT_RELU 1
+#define TTS_ACT_TANH 2
+
+typedef struct TtsAttnW {
+  const void* w_in;   /* bf16 [768][256]  rows 0-255 Wq (pre-scaled by 1/8), 256-511 Wk, 512-767 Wv */
+  const float* b_in;  /* f32  [768]       (q part pre-scaled) */
+  const void* w_out;  /* bf16 [256][256] */
+  const float* b_out; /* f32  [256] */
+} TtsAttnW;
+
+typedef struct TtsFfnW {
+  const void* w1;  const float* b1; /* bf16 [1024][256], f32 [1024] */
+  const void* w2;  const float* b2; /* bf16 [256][1024], f32 [256]  */
+} TtsFfnW;
+
+typedef struct TtsLnW { const float* g; const float* b; } TtsLnW; /* f32 [256] each */
+
+typedef struct TtsEncLayerW { TtsAttnW sa; TtsFfnW ffn; TtsLnW ln1, ln2; } TtsEncLayerW;
+typedef struct TtsDecLayerW { TtsAttnW sa, ca; TtsFfnW ffn; TtsLnW ln1, ln2, ln3; } TtsDecLayerW;
+
+/* All matrices bf16, K-major ([out][in]); conv weights are [out][tap][in_padded] with eval-mode
+ * BatchNorm folded in (model/module.py:19,30); biases / LayerNorm / PE in f32. */
+typedef struct TtsWeights {
+  const void* emb; int32_t n_phon; int32_t reserved0;   /* bf16 [n_phon][256] */
+  const void* enc_conv_w[3]; const float* enc_conv_b[3];/* bf16 [256][5*256] */
+  const void* enc_lin_w; const float* enc_lin_b;        /* bf16 [256][256] */
+  TtsEncLayerW enc[3];
+  const void* pre1_w; const float* pre1_b;              /* bf16 [256][128] (80 mel bins zero padded) */
+  const void* pre2_w; const float* pre2_b;              /* bf16 [256][256] */
+  TtsDecLayerW dec[3];
+  const void* head_w; const float* head_b;              /* bf16 [81][256]: rows 0-79 mel, row 80 stop */
+  const void* post_w[5]; const float* post_b[5];        /* [256][5*128], 3x[256][5*256], [80][5*256] */
+  const float* pe; float alpha; int32_t reserved1;      /* f32 [5000][256]; shared scalar alpha */
+} TtsWeights;
+
+int tts_abi_version(void);
+const char* tts_last_error(void);
+
+/* Bytes of scratch the calls below need for these sizes (Tm = frames; for tts_decode pass max frames). */
+size_t tts_workspace_bytes(int B, int Tp, int Tm);
+
+/* Teacher-forced forward.  phoneme i64 [B][Tp], mel f32 [B][Tm][80], lens i64 [B] (1 <= len <= T).
+ * Outputs f32: mel_pre [B][Tm][80], mel_post [B][Tm][80], stop [B][Tm], align [3][B][4][Tm][Tp]
+ * (align may be NULL unless TTS_FLAG_WANT_ALIGN). */
+int tts_forward(const TtsWeights* w, const int64_t* phoneme, const float* mel, const int64_t* ph_lens,
+                const int64_t* mel_lens, int B, int Tp, int Tm, int flags, float* mel_pre, float* mel_post,
+                float* stop, float* align, void* workspace, size_t ws_bytes, void* stream);
+
+/* Encoder + per-layer cross-attention K/V of the memory.
+ * cross_kv bf16 [3][B][Tp][512] (K cols 0-255, V cols 256-511); ph_len_i32 int32 [B] (clamped copy). */
+int tts_encode(const TtsWeights* w, const int64_t* phoneme, const int64_t* ph_lens, int B, int Tp, int flags,
+               void* cross_kv, int32_t* ph_len_i32, void* workspace, size_t ws_bytes, void* stream);
+
+/* Greedy AR decode, all steps in one launch.  self_kv bf16 [3][B][max_frames][512] scratch;
+ * mel_out f32 [B][max_frames][80], stop_out f32 [B][max_frames]; stop_count int32 [max_frames] scratch;
+ * n_frames int32 [1] (device) receives the number of frames produced under the reference's rule
+ * (first step at which sigmoid(stop) >= threshold for ALL rows, else max_frames).
+ * rows_per_cluster / cluster_size: 0 = choose automatically. */
+int tts_decode(const TtsWeights* w, const void* cross_kv, const int32_t* ph_len_i32, int B, int Tp,
+               int max_frames, float stop_threshold, void* self_kv, float* mel_out, float* stop_out,
+               int32_t* stop_count, int32_t* n_frames, int rows_per_cluster, int cluster_size, void* stream);
+
+/* PostNet with residual: mel_post = PostNet(mel_pre) + mel_pre, f32 [B][T][80] both. */
+int tts_postnet(const TtsWeights* w, const float* mel_pre, int B, int T, float* mel_post, void* workspace,
+                size_t ws_bytes, void* stream);
+
+/* ---- operator-level entry points (used by the parity tests; same kernels as above) ---- */
+
+/* out = epilogue(A[M][K] . W[N][K]^T): +bias, act, +alpha*pe[row % pe_period], +residual, LayerNorm.
+ * A, W, residual, out_bf16 are bf16; bias/pe/ln f32; any of pe/residual/ln_g/out_bf16/out_f32 may be NULL.
+ * K must be a multiple of 64 in memory (zero padded). */
+int tts_op_linear(const void* A, const void* W, const float* bias, int M, int N, int K, int act,
+                  const float* pe, float alpha, int pe_period, const void* residual, const float* ln_g,
+                  const float* ln_b, void* out_bf16, float* out_f32, void* stream);
+
+/* Conv1d(kernel `taps`, zero padding (taps-1)/2) over x bf16 [B][T][C] with W bf16 [N][taps][Cpad]
+ * (Cpad = C rounded up to 64), + bias, act; optional f32 residual [B][T][N]. */
+int tts_op_conv1d(const void* x, const void* W, const float* bias, int B, int T, int C, int N, int taps,
+                  int act, const float* residual_f32, void* out_bf16, float* out_f32, void* stream);
+
+/* Multi-head attention core, 4 heads x 64: q [B][Tq][ldq], k/v [B][Tk][ld] bf16 (q pre-scaled),
+ * klen int32 [B] or NULL, causal 0/1, out bf16 [B][Tq][256], probs f32 [B][4][Tq][Tk] or NULL. */
+int tts_op_attention(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, int B, int Tq,
+                     int Tk, const int32_t* klen, int causal, void* out, float* probs, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TTS_B200_H */

@@ -1,0 +1,252 @@
+"""Drop-in for the reference's `model.TransformerTTS` (model/model.py:138-394) on B200.
+
+Same constructor kwargs, same `forward` / `inference` signatures and output dicts, same `state_dict`
+key names, so `lightning_module.py:30,42,154` can use it unchanged for the no-grad / validation /
+inference passes.  All arithmetic runs in the hand-written CUDA library (libtts_b200.so) through the C ABI
+of include/tts_b200.h; PyTorch only owns the tensors.  There is no CPU path and no autograd: calling
+`forward` in training mode raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Dict, Optional
+
+import torch
+import torch.nn as nn
+
+from . import _ext
+from .weights import D, FFN, KS, MAX_PE, N_MELS, PackedWeights
+
+FLAG_WANT_ALIGN, FLAG_ENC_MASK = 1, 2
+
+
+class _Holder(nn.Module):
+    """Plain container node so that parameter names reproduce the reference's dotted keys."""
+
+
+def _pe_table() -> torch.Tensor:
+    # model/model.py:80-86
+    pos = torch.arange(0, MAX_PE, dtype=torch.float32).unsqueeze(1)
+    div = torch.exp(torch.arange(0, D, 2, dtype=torch.float32) * (-math.log(10000.0)) / D)
+    pe = torch.zeros(MAX_PE, D)
+    pe[:, 0::2] = torch.sin(pos * div)
+    pe[:, 1::2] = torch.cos(pos * div)
+    return pe
+
+
+def _reference_layout_init(n_phon: int) -> Dict[str, torch.Tensor]:
+    """Fresh tensors under the reference's key names with the reference's init laws
+    (model/module.py:21-25,47-50 Xavier-normal with activation gain, zero bias; torch defaults elsewhere)."""
+    sd: Dict[str, torch.Tensor] = {}
+    relu_gain, tanh_gain = math.sqrt(2.0), 5.0 / 3.0
+
+    def xavier(shape, gain):
+        t = torch.empty(shape)
+        nn.init.xavier_normal_(t, gain=gain)
+        return t
+
+    def conv_bn(prefix, cin, cout, gain):
+        sd[f"{prefix}.conv.weight"] = xavier((cout, cin, KS), gain)
+        sd[f"{prefix}.conv.bias"] = torch.zeros(cout)
+        sd[f"{prefix}.bn.weight"] = torch.ones(cout)
+        sd[f"{prefix}.bn.bias"] = torch.zeros(cout)
+        sd[f"{prefix}.bn.running_mean"] = torch.zeros(cout)
+        sd[f"{prefix}.bn.running_var"] = torch.ones(cout)
+        sd[f"{prefix}.bn.num_batches_tracked"] = torch.zeros((), dtype=torch.int64)
+
+    def linear_norm(prefix, cin, cout):
+        sd[f"{prefix}.linear.weight"] = xavier((cout, cin), relu_gain)
+        sd[f"{prefix}.linear.bias"] = torch.zeros(cout)
+
+    def mha(prefix):
+        w = torch.empty(3 * D, D)
+        nn.init.xavier_uniform_(w)
+        sd[f"{prefix}.in_proj_weight"] = w
+        sd[f"{prefix}.in_proj_bias"] = torch.zeros(3 * D)
+        lin = nn.Linear(D, D)
+        sd[f"{prefix}.out_proj.weight"] = lin.weight.detach().clone()
+        sd[f"{prefix}.out_proj.bias"] = torch.zeros(D)
+
+    def ffn_ln(prefix, n_norm):
+        l1, l2 = nn.Linear(D, FFN), nn.Linear(FFN, D)
+        sd[f"{prefix}.linear1.weight"], sd[f"{prefix}.linear1.bias"] = l1.weight.detach().clone(), l1.bias.detach().clone()
+        sd[f"{prefix}.linear2.weight"], sd[f"{prefix}.linear2.bias"] = l2.weight.detach().clone(), l2.bias.detach().clone()
+        for i in range(1, n_norm + 1):
+            sd[f"{prefix}.norm{i}.weight"] = torch.ones(D)
+            sd[f"{prefix}.norm{i}.bias"] = torch.zeros(D)
+
+    sd["emb.weight"] = torch.randn(n_phon, D)
+    for i in range(3):
+        conv_bn(f"enc_prenet.layers.{2 * i}", D, D, relu_gain)
+    linear_norm("enc_prenet.linear", D, D)
+    linear_norm("dec_prenet.linear1", N_MELS, D)
+    linear_norm("dec_prenet.linear2", D, D)
+    sd["pe.alpha"] = torch.ones(1)
+    sd["pe.pe"] = _pe_table()
+    for l in range(3):
+        mha(f"encoder.layers.{l}.self_attn")
+        ffn_ln(f"encoder.layers.{l}", 2)
+    for l in range(3):
+        mha(f"decoder.layers.{l}.self_attn")
+        mha(f"decoder.layers.{l}.multihead_attn")
+        ffn_ln(f"decoder.layers.{l}", 3)
+    chans = [N_MELS, D, D, D, D, N_MELS]
+    for i in range(5):
+        conv_bn(f"postnet.layers.{3 * i}", chans[i], chans[i + 1], tanh_gain)
+    linear_norm("linear1", D, N_MELS)
+    linear_norm("linear2", D, 1)
+    return sd
+
+
+_BUFFER_SUFFIXES = ("running_mean", "running_var", "num_batches_tracked", "pe.pe")
+
+
+class TransformerTTS(nn.Module):
+    """B200 replacement for model/model.py:138 `TransformerTTS` (eval-mode forward and AR inference)."""
+
+    def __init__(self, encoder_prenet_n_layers=3, encoder_prenet_in_channel=256, encoder_prenet_out_channel=256,
+                 encoder_prenet_kernel_size=5, encoder_prenet_dropout=0.5, encoder_n_layers=3, encoder_n_head=4,
+                 encoder_d_ffn=1024, encoder_dropout=0.1, decoder_n_layers=3, decoder_n_head=4, decoder_d_ffn=1024,
+                 decoder_dropout=0.1, postnet_n_layers=5, postnet_kernel_size=5, postnet_dropout=0.5, d_model=256,
+                 n_phon=100, n_mels=80, device="cuda"):
+        super().__init__()
+        got = dict(encoder_prenet_n_layers=encoder_prenet_n_layers, encoder_prenet_in_channel=encoder_prenet_in_channel,
+                   encoder_prenet_out_channel=encoder_prenet_out_channel,
+                   encoder_prenet_kernel_size=encoder_prenet_kernel_size, encoder_n_layers=encoder_n_layers,
+                   encoder_n_head=encoder_n_head, encoder_d_ffn=encoder_d_ffn, decoder_n_layers=decoder_n_layers,
+                   decoder_n_head=decoder_n_head, decoder_d_ffn=decoder_d_ffn, postnet_n_layers=postnet_n_layers,
+                   postnet_kernel_size=postnet_kernel_size, d_model=d_model, n_mels=n_mels)
+        want = dict(encoder_prenet_n_layers=3, encoder_prenet_in_channel=256, encoder_prenet_out_channel=256,
+                    encoder_prenet_kernel_size=5, encoder_n_layers=3, encoder_n_head=4, encoder_d_ffn=1024,
+                    decoder_n_layers=3, decoder_n_head=4, decoder_d_ffn=1024, postnet_n_layers=5,
+                    postnet_kernel_size=5, d_model=256, n_mels=80)
+        bad = {k: v for k, v in got.items() if want[k] != v}
+        if bad:
+            raise ValueError(f"the sm_100a kernels are specialised to config.yaml:25-42; unsupported values: {bad}")
+        self.device = torch.device(device)
+        self.n_phon = n_phon
+        self.strict_lens = False      # True: reproduce the reference's Tp == max(lens) assert (costs a host sync)
+        for key, t in _reference_layout_init(n_phon).items():
+            self._register(key, t.to(self.device))
+        self._packed: Optional[PackedWeights] = None
+        self._ws = None
+        self.register_load_state_dict_post_hook(lambda module, incompatible: module.refresh_weights())
+
+    # ------------------------------------------------------------------ parameter tree
+    def _register(self, key: str, t: torch.Tensor):
+        node = self
+        parts = key.split(".")
+        for p in parts[:-1]:
+            if not hasattr(node, p):
+                node.add_module(p, _Holder())
+            node = getattr(node, p)
+        if key.endswith(_BUFFER_SUFFIXES):
+            node.register_buffer(parts[-1], t)
+        else:
+            node.register_parameter(parts[-1], nn.Parameter(t, requires_grad=t.is_floating_point()))
+
+    @classmethod
+    def from_reference(cls, module_or_state_dict, device="cuda") -> "TransformerTTS":
+        """Build from a reference `model.TransformerTTS` instance or its state_dict (same key names)."""
+        sd = module_or_state_dict if isinstance(module_or_state_dict, dict) else module_or_state_dict.state_dict()
+        m = cls(n_phon=sd["emb.weight"].shape[0], device=device)
+        m.load_state_dict(sd, strict=True)
+        return m.eval()
+
+    def refresh_weights(self):
+        """Drop the packed (bf16 / BN-folded) device copies; they are rebuilt from the parameters on next use."""
+        self._packed = None
+
+    def _weights(self) -> PackedWeights:
+        if self._packed is None:
+            self._packed = PackedWeights(self.state_dict(), self.device)
+        return self._packed
+
+    def _workspace(self, B, Tp, Tm):
+        need = _ext.load().tts_workspace_bytes(B, Tp, Tm) + 1024
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        base = self._ws.data_ptr()
+        aligned = (base + 1023) & ~1023
+        return C.c_void_p(aligned), self._ws.numel() - (aligned - base)
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _prep(self, t, dtype):
+        return t.to(device=self.device, dtype=dtype, non_blocking=True).contiguous()
+
+    # ------------------------------------------------------------------ model/model.py:260-320
+    def forward(self, phoneme, melspec, phoneme_lens, melspec_lens, return_alignments: bool = True):
+        if self.training:
+            raise RuntimeError("transformertts_b200 accelerates eval-mode forward only (dropout off, BatchNorm running "
+                               "statistics); call .eval() first. Training-mode forward/backward is out of scope.")
+        lib = _ext.load()
+        phoneme, phoneme_lens = self._prep(phoneme, torch.int64), self._prep(phoneme_lens, torch.int64)
+        melspec, melspec_lens = self._prep(melspec, torch.float32), self._prep(melspec_lens, torch.int64)
+        if phoneme.dim() != 2 or melspec.dim() != 3 or melspec.shape[2] != N_MELS:
+            raise ValueError("expected phoneme [B,Tp] and melspec [B,Tm,80]")
+        B, Tp = phoneme.shape
+        Tm = melspec.shape[1]
+        if melspec.shape[0] != B or phoneme_lens.shape != (B,) or melspec_lens.shape != (B,):
+            raise ValueError("batch sizes of phoneme / melspec / lens disagree")
+        if self.strict_lens:   # model/model.py:294 asserts the mask width equals the padded length
+            assert int(phoneme_lens.max()) == Tp and int(melspec_lens.max()) == Tm, "Size mismatch between memory and mask"
+        with torch.cuda.device(self.device):
+            w = self._weights()
+            ws, ws_bytes = self._workspace(B, Tp, Tm)
+            pred = torch.empty(B, Tm, N_MELS, dtype=torch.float32, device=self.device)
+            post = torch.empty_like(pred)
+            stop = torch.empty(B, Tm, dtype=torch.float32, device=self.device)
+            align = torch.empty(3, B, 4, Tm, Tp, dtype=torch.float32, device=self.device) if return_alignments else None
+            flags = FLAG_ENC_MASK | (FLAG_WANT_ALIGN if return_alignments else 0)
+            _ext.check(lib.tts_forward(C.byref(w.struct), _ext.ptr(phoneme), _ext.ptr(melspec), _ext.ptr(phoneme_lens),
+                                       _ext.ptr(melspec_lens), B, Tp, Tm, flags, _ext.ptr(pred), _ext.ptr(post),
+                                       _ext.ptr(stop), _ext.ptr(align), ws, ws_bytes, self._stream()), "tts_forward")
+        return {
+            "pred_melspec": pred,
+            "post_melspec": post,
+            "pred_stop": stop,
+            "alignments": [align[l] for l in range(3)] if return_alignments else [],
+        }
+
+    # ------------------------------------------------------------------ model/model.py:323-394
+    @torch.no_grad()
+    def inference(self, phoneme, phoneme_lens, max_len: int = 1500, stop_threshold: float = 0.5,
+                  rows_per_cluster: int = 0, cluster_size: int = 0):
+        self.eval()                                   # model/model.py:342
+        lib = _ext.load()
+        phoneme, phoneme_lens = self._prep(phoneme, torch.int64), self._prep(phoneme_lens, torch.int64)
+        if phoneme.dim() != 2 or phoneme_lens.shape != (phoneme.shape[0],):
+            raise ValueError("expected phoneme [B,Tp] and phoneme_lens [B]")
+        B, Tp = phoneme.shape
+        max_frames = int(max_len) - 1                 # `for t in range(1, max_len)`  model/model.py:354
+        if max_frames < 1:
+            raise ValueError("max_len must be >= 2 (the reference produces at most max_len-1 frames)")
+        dev = self.device
+        with torch.cuda.device(dev):
+            w = self._weights()
+            ws, ws_bytes = self._workspace(B, Tp, 1)
+            cross_kv = torch.empty(3 * B * Tp * 512, dtype=torch.bfloat16, device=dev)
+            ph_len = torch.empty(B, dtype=torch.int32, device=dev)
+            # encoder WITHOUT key-padding mask (model/model.py:346-348)
+            _ext.check(lib.tts_encode(C.byref(w.struct), _ext.ptr(phoneme), _ext.ptr(phoneme_lens), B, Tp, 0,
+                                      _ext.ptr(cross_kv), _ext.ptr(ph_len), ws, ws_bytes, self._stream()), "tts_encode")
+            self_kv = torch.empty(3 * B * max_frames * 512, dtype=torch.bfloat16, device=dev)
+            mel = torch.empty(B, max_frames, N_MELS, dtype=torch.float32, device=dev)
+            stop = torch.empty(B, max_frames, dtype=torch.float32, device=dev)
+            stop_count = torch.empty(max_frames, dtype=torch.int32, device=dev)
+            n_frames = torch.empty(1, dtype=torch.int32, device=dev)
+            _ext.check(lib.tts_decode(C.byref(w.struct), _ext.ptr(cross_kv), _ext.ptr(ph_len), B, Tp, max_frames,
+                                      float(stop_threshold), _ext.ptr(self_kv), _ext.ptr(mel), _ext.ptr(stop),
+                                      _ext.ptr(stop_count), _ext.ptr(n_frames), int(rows_per_cluster),
+                                      int(cluster_size), self._stream()), "tts_decode")
+            n = int(n_frames.item())                  # the single host sync of the AR loop
+            pred = mel[:, :n].contiguous()
+            pred_stop = stop[:, :n].unsqueeze(-1).contiguous()     # (B,T,1)  model/model.py:378,393
+            post = torch.empty_like(pred)
+            ws, ws_bytes = self._workspace(B, 1, n)
+            _ext.check(lib.tts_postnet(C.byref(w.struct), _ext.ptr(pred), B, n, _ext.ptr(post), ws, ws_bytes,
+                                       self._stream()), "tts_postnet")
+        return {"pred_melspec": pred, "post_melspec": post, "pred_stop": pred_stop}

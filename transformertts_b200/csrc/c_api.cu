@@ -1,0 +1,409 @@
+// extern "C" boundary (include/tts_b200.h) and the orchestration of the hot path:
+// TransformerTTS.forward (model/model.py:260-320) and .inference (model/model.py:323-394) as sequences
+// of the kernels in gemm.cu / attention.cu / decode.cu over a caller-provided workspace.
+#include "../../include/tts_b200.h"
+
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "decode.cuh"
+#include "kernels.h"
+
+using namespace tts;
+
+static thread_local char g_err[512] = "";
+
+static int fail(const char* msg) {
+  snprintf(g_err, sizeof(g_err), "%s", msg);
+  return 1;
+}
+#define TRY(expr)                                  \
+  do {                                             \
+    const char* _e = (expr);                       \
+    if (_e != nullptr) return fail(_e);            \
+  } while (0)
+
+// ------------------------------------------------------------------ small kernels
+namespace tts {
+
+__global__ void embed_kernel(const int64_t* __restrict__ ph, const uint4* __restrict__ table, uint4* __restrict__ out,
+                             int n_tok, int n_phon) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;      // one 16-byte chunk (8 channels) per thread
+  if (i >= n_tok * 32) return;
+  const int tok = i >> 5, ch = i & 31;
+  long long id = ph[tok];
+  id = id < 0 ? 0 : (id >= n_phon ? n_phon - 1 : id);
+  out[i] = __ldg(table + id * 32 + ch);
+}
+
+__global__ void cast_mel_kernel(const float* __restrict__ in, bf16* __restrict__ out, size_t n) {
+  const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i + 4 <= n) {
+    const float4 v = *reinterpret_cast<const float4*>(in + i);
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    uint2 u;
+    u.x = *reinterpret_cast<uint32_t*>(&a);
+    u.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(out + i) = u;
+  } else {
+    for (size_t j = i; j < n; ++j) out[j] = __float2bfloat16(in[j]);
+  }
+}
+
+__global__ void lens_kernel(const int64_t* __restrict__ in, int* __restrict__ out, int n, int lo, int hi) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    long long v = in[i];
+    out[i] = (int)(v < lo ? lo : (v > hi ? hi : v));
+  }
+}
+
+const char* embed_launch(const int64_t* phoneme, const bf16* table, bf16* out, int n_tok, int n_phon, cudaStream_t s) {
+  const int n = n_tok * 32;
+  embed_kernel<<<(n + 255) / 256, 256, 0, s>>>(phoneme, reinterpret_cast<const uint4*>(table),
+                                                reinterpret_cast<uint4*>(out), n_tok, n_phon);
+  return cudaGetLastError() == cudaSuccess ? nullptr : "embedding kernel launch failed";
+}
+const char* cast_mel_launch(const float* mel, bf16* out, size_t n, cudaStream_t s) {
+  const size_t thr = (n + 3) / 4;
+  cast_mel_kernel<<<(unsigned)((thr + 255) / 256), 256, 0, s>>>(mel, out, n);
+  return cudaGetLastError() == cudaSuccess ? nullptr : "cast kernel launch failed";
+}
+const char* lens_launch(const int64_t* in, int* out, int n, int lo, int hi, cudaStream_t s) {
+  lens_kernel<<<(n + 127) / 128, 128, 0, s>>>(in, out, n, lo, hi);
+  return cudaGetLastError() == cudaSuccess ? nullptr : "lens kernel launch failed";
+}
+
+}  // namespace tts
+
+// ------------------------------------------------------------------ argument builders
+static GemmArgs linear_args(const bf16* A, int M, int K, const void* W, const float* bias, int N) {
+  GemmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.A = A; g.B = 1; g.T = M; g.C = K;
+  g.W = reinterpret_cast<const bf16*>(W); g.N = N;
+  g.taps = 1; g.tap_off = 0; g.kc_per_tap = (K + 63) / 64;
+  g.bias = bias;
+  return g;
+}
+static GemmArgs conv_args(const bf16* x, int B, int T, int C, const void* W, const float* bias, int N, int taps,
+                          int tap_off) {
+  GemmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.A = x; g.B = B; g.T = T; g.C = C;
+  g.W = reinterpret_cast<const bf16*>(W); g.N = N;
+  g.taps = taps; g.tap_off = tap_off; g.kc_per_tap = (C + 63) / 64;
+  g.bias = bias;
+  return g;
+}
+
+// carve 1 KiB aligned regions out of the caller's workspace
+struct Carver {
+  uint8_t* base; size_t off; size_t cap;
+  void* take(size_t bytes) {
+    void* p = base + off;
+    off += (bytes + 1023) & ~size_t(1023);
+    return p;
+  }
+};
+
+struct Workspace {
+  int* ph_len; int* mel_len;
+  bf16 *e0, *e1, *qkv_e, *att_e, *ffn_e;         // encoder side  [Np][...]
+  bf16 *mel_in, *d0, *d1, *qkv_d, *att_d, *ffn_d, *cq, *ckv, *mel_pre16;
+  size_t total;
+};
+
+static Workspace carve(void* base, int B, int Tp, int Tm) {
+  const size_t Np = (size_t)B * Tp, Nm = (size_t)B * (Tm > 0 ? Tm : 1);
+  Carver c{reinterpret_cast<uint8_t*>(base), 0, 0};
+  Workspace w;
+  w.ph_len = (int*)c.take(sizeof(int) * B);
+  w.mel_len = (int*)c.take(sizeof(int) * B);
+  w.e0 = (bf16*)c.take(Np * kD * 2);
+  w.e1 = (bf16*)c.take(Np * kD * 2);
+  w.qkv_e = (bf16*)c.take(Np * 3 * kD * 2);
+  w.att_e = (bf16*)c.take(Np * kD * 2);
+  w.ffn_e = (bf16*)c.take(Np * kF * 2);
+  w.ckv = (bf16*)c.take(Np * 2 * kD * 2);
+  w.mel_in = (bf16*)c.take(Nm * kMel * 2);
+  w.mel_pre16 = (bf16*)c.take(Nm * kMel * 2);
+  w.d0 = (bf16*)c.take(Nm * kD * 2);
+  w.d1 = (bf16*)c.take(Nm * kD * 2);
+  w.qkv_d = (bf16*)c.take(Nm * 3 * kD * 2);
+  w.att_d = (bf16*)c.take(Nm * kD * 2);
+  w.cq = (bf16*)c.take(Nm * kD * 2);
+  w.ffn_d = (bf16*)c.take(Nm * kF * 2);
+  w.total = c.off;
+  return w;
+}
+
+extern "C" int tts_abi_version(void) { return TTS_ABI_VERSION; }
+extern "C" const char* tts_last_error(void) { return g_err; }
+extern "C" size_t tts_workspace_bytes(int B, int Tp, int Tm) {
+  if (B <= 0 || Tp <= 0 || Tm < 0) return 0;
+  return carve(nullptr, B, Tp, Tm).total;
+}
+
+// ------------------------------------------------------------------ operator-level entry points
+extern "C" int tts_op_linear(const void* A, const void* W, const float* bias, int M, int N, int K, int act,
+                             const float* pe, float alpha, int pe_period, const void* residual, const float* ln_g,
+                             const float* ln_b, void* out_bf16, float* out_f32, void* stream) {
+  if (K % 64 != 0) return fail("tts_op_linear: K must be a multiple of 64");
+  GemmArgs g = linear_args((const bf16*)A, M, K, W, bias, N);
+  g.act = act;
+  g.pe = pe; g.alpha = alpha; g.pe_period = pe_period;
+  g.residual = (const bf16*)residual; g.ld_res = N;
+  g.ln_g = ln_g; g.ln_b = ln_b;
+  g.out_bf16 = (bf16*)out_bf16; g.ld_bf16 = N;
+  g.out_f32 = out_f32; g.ld_f32 = N;
+  TRY(gemm_launch(g, (cudaStream_t)stream));
+  return 0;
+}
+
+extern "C" int tts_op_conv1d(const void* x, const void* W, const float* bias, int B, int T, int C, int N, int taps,
+                             int act, const float* residual_f32, void* out_bf16, float* out_f32, void* stream) {
+  GemmArgs g = conv_args((const bf16*)x, B, T, C, W, bias, N, taps, -((taps - 1) / 2));
+  g.act = act;
+  g.residual_f32 = residual_f32; g.ld_res32 = N;
+  g.out_bf16 = (bf16*)out_bf16; g.ld_bf16 = N;
+  g.out_f32 = out_f32; g.ld_f32 = N;
+  TRY(gemm_launch(g, (cudaStream_t)stream));
+  return 0;
+}
+
+extern "C" int tts_op_attention(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, int B, int Tq,
+                                int Tk, const int32_t* klen, int causal, void* out, float* probs, void* stream) {
+  AttnArgs a;
+  a.Q = (const bf16*)q; a.ldq = ldq;
+  a.K = (const bf16*)k; a.ldk = ldk;
+  a.V = (const bf16*)v; a.ldv = ldv;
+  a.O = (bf16*)out; a.ldo = kD;
+  a.probs = probs; a.klen = klen;
+  a.B = B; a.Tq = Tq; a.Tk = Tk; a.causal = causal;
+  TRY(attn_launch(a, (cudaStream_t)stream));
+  return 0;
+}
+
+// ------------------------------------------------------------------ shared pieces of forward / inference
+static const char* run_attention(const bf16* q, int ldq, const bf16* k, const bf16* v, int ldkv, bf16* out, float* probs,
+                                 const int* klen, int B, int Tq, int Tk, int causal, cudaStream_t s) {
+  AttnArgs a;
+  a.Q = q; a.ldq = ldq; a.K = k; a.ldk = ldkv; a.V = v; a.ldv = ldkv;
+  a.O = out; a.ldo = kD; a.probs = probs; a.klen = klen;
+  a.B = B; a.Tq = Tq; a.Tk = Tk; a.causal = causal;
+  return attn_launch(a, s);
+}
+
+// out = LayerNorm(res + A . W^T + b)
+static const char* proj_res_ln(const bf16* A, int M, int K, const void* W, const float* b, const bf16* res,
+                               const TtsLnW& ln, bf16* out, cudaStream_t s) {
+  GemmArgs g = linear_args(A, M, K, W, b, kD);
+  g.residual = res; g.ld_res = kD;
+  g.ln_g = ln.g; g.ln_b = ln.b;
+  g.out_bf16 = out; g.ld_bf16 = kD;
+  return gemm_launch(g, s);
+}
+
+static const char* proj(const bf16* A, int M, int K, const void* W, const float* b, int N, int act, bf16* out,
+                        cudaStream_t s) {
+  GemmArgs g = linear_args(A, M, K, W, b, N);
+  g.act = act;
+  g.out_bf16 = out; g.ld_bf16 = N;
+  return gemm_launch(g, s);
+}
+
+// emb -> EncoderPreNet -> PE -> 3 post-norm encoder layers (model/model.py:288-292 / 345-348).
+// Result (memory) is left in ws.e0.
+static const char* run_encoder(const TtsWeights* w, const int64_t* phoneme, int B, int Tp, bool masked, Workspace& ws,
+                               cudaStream_t s) {
+  const int Np = B * Tp;
+  const char* e;
+  if ((e = embed_launch(phoneme, (const bf16*)w->emb, ws.e0, Np, w->n_phon, s))) return e;
+  bf16* cur = ws.e0; bf16* nxt = ws.e1;
+  for (int i = 0; i < 3; ++i) {                       // Conv1d k5 + folded BN, no activation
+    GemmArgs g = conv_args(cur, B, Tp, kD, w->enc_conv_w[i], w->enc_conv_b[i], kD, kTaps, -(kTaps - 1) / 2);
+    g.out_bf16 = nxt; g.ld_bf16 = kD;
+    if ((e = gemm_launch(g, s))) return e;
+    bf16* t = cur; cur = nxt; nxt = t;
+  }
+  {                                                   // Linear + alpha * PE  (cur == e1 -> e0)
+    GemmArgs g = linear_args(cur, Np, kD, w->enc_lin_w, w->enc_lin_b, kD);
+    g.pe = w->pe; g.alpha = w->alpha; g.pe_period = Tp;
+    g.out_bf16 = nxt; g.ld_bf16 = kD;
+    if ((e = gemm_launch(g, s))) return e;
+    bf16* t = cur; cur = nxt; nxt = t;
+  }
+  for (int l = 0; l < 3; ++l) {
+    const TtsEncLayerW& L = w->enc[l];
+    if ((e = proj(cur, Np, kD, L.sa.w_in, L.sa.b_in, 3 * kD, ACT_NONE, ws.qkv_e, s))) return e;
+    if ((e = run_attention(ws.qkv_e, 3 * kD, ws.qkv_e + kD, ws.qkv_e + 2 * kD, 3 * kD, ws.att_e, nullptr,
+                           masked ? ws.ph_len : nullptr, B, Tp, Tp, 0, s))) return e;
+    if ((e = proj_res_ln(ws.att_e, Np, kD, L.sa.w_out, L.sa.b_out, cur, L.ln1, nxt, s))) return e;
+    if ((e = proj(nxt, Np, kD, L.ffn.w1, L.ffn.b1, kF, ACT_RELU, ws.ffn_e, s))) return e;
+    if ((e = proj_res_ln(ws.ffn_e, Np, kF, L.ffn.w2, L.ffn.b2, nxt, L.ln2, cur, s))) return e;
+  }
+  return cur == ws.e0 ? nullptr : "internal: encoder output buffer parity";
+}
+
+// cross-attention K/V of the memory for decoder layer l: [Np][512]
+static const char* run_cross_kv(const TtsWeights* w, int l, const bf16* memory, int Np, bf16* out, cudaStream_t s) {
+  const TtsAttnW& ca = w->dec[l].ca;
+  return proj(memory, Np, kD, (const bf16*)ca.w_in + (size_t)kD * kD, ca.b_in + kD, 2 * kD, ACT_NONE, out, s);
+}
+
+// PostNet (model/model.py:129-135) + residual (:310): 4 x tanh(BN(conv)), BN(conv), + mel_pre
+static const char* run_postnet(const TtsWeights* w, const bf16* mel16, const float* mel_pre, int B, int T, bf16* p0,
+                               bf16* p1, float* mel_post, cudaStream_t s) {
+  const char* e;
+  GemmArgs g = conv_args(mel16, B, T, kMel, w->post_w[0], w->post_b[0], kD, kTaps, -(kTaps - 1) / 2);
+  g.act = ACT_TANH; g.out_bf16 = p0; g.ld_bf16 = kD;
+  if ((e = gemm_launch(g, s))) return e;
+  bf16* cur = p0; bf16* nxt = p1;
+  for (int i = 1; i < 4; ++i) {
+    GemmArgs h = conv_args(cur, B, T, kD, w->post_w[i], w->post_b[i], kD, kTaps, -(kTaps - 1) / 2);
+    h.act = ACT_TANH; h.out_bf16 = nxt; h.ld_bf16 = kD;
+    if ((e = gemm_launch(h, s))) return e;
+    bf16* t = cur; cur = nxt; nxt = t;
+  }
+  GemmArgs f = conv_args(cur, B, T, kD, w->post_w[4], w->post_b[4], kMel, kTaps, -(kTaps - 1) / 2);
+  f.residual_f32 = mel_pre; f.ld_res32 = kMel;
+  f.out_f32 = mel_post; f.ld_f32 = kMel;
+  return gemm_launch(f, s);
+}
+
+static int check_common(const TtsWeights* w, int B, int Tp, int Tm, const void* ws, size_t ws_bytes) {
+  if (w == nullptr) return fail("weights pointer is NULL");
+  if (B <= 0 || Tp <= 0 || Tm <= 0) return fail("B, Tp and Tm must be positive");
+  if (Tp > kPeMax || Tm > kPeMax) return fail("sequence longer than the positional-encoding table (5000)");
+  if (ws == nullptr || ws_bytes < tts_workspace_bytes(B, Tp, Tm)) return fail("workspace too small");
+  if ((reinterpret_cast<uintptr_t>(ws) & 1023) != 0) return fail("workspace must be 1024-byte aligned");
+  return 0;
+}
+
+// ------------------------------------------------------------------ TransformerTTS.forward
+extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const float* mel, const int64_t* ph_lens,
+                           const int64_t* mel_lens, int B, int Tp, int Tm, int flags, float* mel_pre, float* mel_post,
+                           float* stop, float* align, void* workspace, size_t ws_bytes, void* stream) {
+  if (check_common(w, B, Tp, Tm, workspace, ws_bytes)) return 1;
+  if ((flags & TTS_FLAG_WANT_ALIGN) && align == nullptr) return fail("WANT_ALIGN set but align is NULL");
+  cudaStream_t s = (cudaStream_t)stream;
+  Workspace ws = carve(workspace, B, Tp, Tm);
+  const int Np = B * Tp, Nm = B * Tm;
+  TRY(lens_launch(ph_lens, ws.ph_len, B, 1, Tp, s));
+  TRY(lens_launch(mel_lens, ws.mel_len, B, 1, Tm, s));
+  TRY(run_encoder(w, phoneme, B, Tp, (flags & TTS_FLAG_ENC_MASK) != 0, ws, s));
+  const bf16* memory = ws.e0;
+
+  // decoder prenet on the go-frame-shifted target (model/model.py:278-279, 297): frame t reads mel[t-1]
+  TRY(cast_mel_launch(mel, ws.mel_in, (size_t)Nm * kMel, s));
+  {
+    GemmArgs g = conv_args(ws.mel_in, B, Tm, kMel, w->pre1_w, w->pre1_b, kD, 1, -1);
+    g.act = ACT_RELU; g.out_bf16 = ws.d0; g.ld_bf16 = kD;
+    TRY(gemm_launch(g, s));
+    GemmArgs h = linear_args(ws.d0, Nm, kD, w->pre2_w, w->pre2_b, kD);
+    h.act = ACT_RELU; h.pe = w->pe; h.alpha = w->alpha; h.pe_period = Tm;
+    h.out_bf16 = ws.d1; h.ld_bf16 = kD;
+    TRY(gemm_launch(h, s));
+  }
+  bf16* x = ws.d1; bf16* y = ws.d0;
+  for (int l = 0; l < 3; ++l) {                      // model/layers.py:46-50 (post-norm)
+    const TtsDecLayerW& L = w->dec[l];
+    TRY(proj(x, Nm, kD, L.sa.w_in, L.sa.b_in, 3 * kD, ACT_NONE, ws.qkv_d, s));
+    TRY(run_attention(ws.qkv_d, 3 * kD, ws.qkv_d + kD, ws.qkv_d + 2 * kD, 3 * kD, ws.att_d, nullptr, ws.mel_len, B, Tm,
+                      Tm, 1, s));
+    TRY(proj_res_ln(ws.att_d, Nm, kD, L.sa.w_out, L.sa.b_out, x, L.ln1, y, s));            // y = LN1
+    TRY(proj(y, Nm, kD, L.ca.w_in, L.ca.b_in, kD, ACT_NONE, ws.cq, s));
+    TRY(run_cross_kv(w, l, memory, Np, ws.ckv, s));
+    float* probs = (flags & TTS_FLAG_WANT_ALIGN) ? align + (size_t)l * B * kH * Tm * Tp : nullptr;
+    TRY(run_attention(ws.cq, kD, ws.ckv, ws.ckv + kD, 2 * kD, ws.att_d, probs, ws.ph_len, B, Tm, Tp, 0, s));
+    TRY(proj_res_ln(ws.att_d, Nm, kD, L.ca.w_out, L.ca.b_out, y, L.ln2, x, s));            // x = LN2
+    TRY(proj(x, Nm, kD, L.ffn.w1, L.ffn.b1, kF, ACT_RELU, ws.ffn_d, s));
+    TRY(proj_res_ln(ws.ffn_d, Nm, kF, L.ffn.w2, L.ffn.b2, x, L.ln3, y, s));                // y = LN3
+    bf16* t = x; x = y; y = t;
+  }
+  {                                                  // mel + stop heads (model/model.py:309,313)
+    GemmArgs g = linear_args(x, Nm, kD, w->head_w, w->head_b, kMel + 1);
+    g.out_f32 = mel_pre; g.ld_f32 = kMel;
+    g.out_bf16 = ws.mel_pre16; g.ld_bf16 = kMel;
+    g.out_last = stop;
+    TRY(gemm_launch(g, s));
+  }
+  TRY(run_postnet(w, ws.mel_pre16, mel_pre, B, Tm, ws.qkv_d, ws.ffn_d, mel_post, s));
+  return 0;
+}
+
+// ------------------------------------------------------------------ TransformerTTS.inference pieces
+extern "C" int tts_encode(const TtsWeights* w, const int64_t* phoneme, const int64_t* ph_lens, int B, int Tp, int flags,
+                          void* cross_kv, int32_t* ph_len_i32, void* workspace, size_t ws_bytes, void* stream) {
+  if (check_common(w, B, Tp, 1, workspace, ws_bytes)) return 1;
+  if (cross_kv == nullptr || ph_len_i32 == nullptr) return fail("tts_encode: output pointer is NULL");
+  cudaStream_t s = (cudaStream_t)stream;
+  Workspace ws = carve(workspace, B, Tp, 1);
+  TRY(lens_launch(ph_lens, ws.ph_len, B, 1, Tp, s));
+  TRY(lens_launch(ph_lens, ph_len_i32, B, 1, Tp, s));
+  TRY(run_encoder(w, phoneme, B, Tp, (flags & TTS_FLAG_ENC_MASK) != 0, ws, s));
+  const int Np = B * Tp;
+  for (int l = 0; l < 3; ++l)
+    TRY(run_cross_kv(w, l, ws.e0, Np, (bf16*)cross_kv + (size_t)l * Np * 2 * kD, s));
+  return 0;
+}
+
+extern "C" int tts_decode(const TtsWeights* w, const void* cross_kv, const int32_t* ph_len_i32, int B, int Tp,
+                          int max_frames, float stop_threshold, void* self_kv, float* mel_out, float* stop_out,
+                          int32_t* stop_count, int32_t* n_frames, int rows_per_cluster, int cluster_size, void* stream) {
+  if (w == nullptr) return fail("weights pointer is NULL");
+  if (B <= 0 || Tp <= 0 || max_frames <= 0) return fail("B, Tp and max_frames must be positive");
+  if (max_frames > kPeMax) return fail("max_frames exceeds the positional-encoding table (5000)");
+  cudaStream_t s = (cudaStream_t)stream;
+  DecodeArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int l = 0; l < 3; ++l) {
+    const TtsDecLayerW& L = w->dec[l];
+    DecLayerW& d = a.layer[l];
+    d.w_qkv = (const bf16*)L.sa.w_in; d.b_qkv = L.sa.b_in;
+    d.w_so = (const bf16*)L.sa.w_out; d.b_so = L.sa.b_out;
+    d.ln1_g = L.ln1.g; d.ln1_b = L.ln1.b;
+    d.w_cq = (const bf16*)L.ca.w_in; d.b_cq = L.ca.b_in;
+    d.w_co = (const bf16*)L.ca.w_out; d.b_co = L.ca.b_out;
+    d.ln2_g = L.ln2.g; d.ln2_b = L.ln2.b;
+    d.w_f1 = (const bf16*)L.ffn.w1; d.b_f1 = L.ffn.b1;
+    d.w_f2 = (const bf16*)L.ffn.w2; d.b_f2 = L.ffn.b2;
+    d.ln3_g = L.ln3.g; d.ln3_b = L.ln3.b;
+  }
+  a.w_pre1 = (const bf16*)w->pre1_w; a.b_pre1 = w->pre1_b;
+  a.w_pre2 = (const bf16*)w->pre2_w; a.b_pre2 = w->pre2_b;
+  a.w_head = (const bf16*)w->head_w; a.b_head = w->head_b;
+  a.pe = w->pe; a.alpha = w->alpha;
+  a.cross_kv = (const bf16*)cross_kv;
+  a.self_kv = (bf16*)self_kv;
+  a.ph_len = ph_len_i32;
+  a.B = B; a.Tp = Tp; a.Tmax = max_frames;
+  // sigmoid(z) >= thr  <=>  z >= logit(thr)   (model/model.py:382-383)
+  if (stop_threshold <= 0.f) a.stop_logit = -INFINITY;
+  else if (stop_threshold >= 1.f) a.stop_logit = INFINITY;
+  else a.stop_logit = (float)log((double)stop_threshold / (1.0 - (double)stop_threshold));
+  a.mel_out = mel_out; a.stop_out = stop_out; a.stop_count = stop_count; a.n_frames = n_frames;
+  if (cudaMemsetAsync(stop_count, 0, sizeof(int) * (size_t)max_frames, s) != cudaSuccess)
+    return fail("cudaMemsetAsync(stop_count) failed");
+  int C = cluster_size > 0 ? cluster_size : 16;
+  int R = rows_per_cluster;
+  if (R <= 0) {                                      // fewest rows per cluster that still fits one wave
+    const int max_clusters = 148 / C;                // upper bound; GPC packing may allow fewer
+    R = 1;
+    while (R < 8 && (B + R - 1) / R > (C == 16 ? 8 : max_clusters)) R *= 2;
+  }
+  TRY(decode_launch(a, R, C, s));
+  return 0;
+}
+
+extern "C" int tts_postnet(const TtsWeights* w, const float* mel_pre, int B, int T, float* mel_post, void* workspace,
+                           size_t ws_bytes, void* stream) {
+  if (check_common(w, B, 1, T, workspace, ws_bytes)) return 1;
+  cudaStream_t s = (cudaStream_t)stream;
+  Workspace ws = carve(workspace, B, 1, T);
+  TRY(cast_mel_launch(mel_pre, ws.mel_pre16, (size_t)B * T * kMel, s));
+  TRY(run_postnet(w, ws.mel_pre16, mel_pre, B, T, ws.qkv_d, ws.ffn_d, mel_post, s));
+  return 0;
+}

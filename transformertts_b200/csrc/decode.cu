@@ -1,0 +1,445 @@
+// Persistent autoregressive greedy mel decode with a per-layer K/V cache (sm_100a).
+//
+// Replaces the loop of TransformerTTS.inference (model/model.py:354-384).  The reference re-runs
+// prenet + PE + all decoder layers over the whole prefix every step and syncs with the host three
+// times per step; here ONE kernel launch runs all steps.  A thread-block cluster owns R utterances:
+// every CTA keeps the R x 256 fp32 residual stream in shared memory, computes a 1/C slice of each
+// projection (bf16 weights streamed from L2, warp-shuffle reductions), and publishes the slice into the
+// shared memory of all C CTAs of the cluster (DSMEM), so one barrier.cluster per phase replaces a kernel
+// boundary.  Attention over the cache is split over heads x key ranges across the CTAs with 16-byte
+// coalesced K/V reads and an online softmax; partial (max, sum, o) triples are combined after the
+// barrier.  The stop rule ("all rows >= threshold at the same step", model/model.py:382-384) is evaluated
+// on the device through a per-step counter; no host round trip happens inside the loop.
+#include <cooperative_groups.h>
+
+#include "decode.cuh"
+#include "ptx.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace tts {
+
+constexpr int DEC_THREADS = 256;
+constexpr int DEC_WARPS = DEC_THREADS / 32;
+constexpr int LDA = 1024;          // floats per row of the broadcast buffers
+constexpr int PSTRIDE = 68;        // floats per attention partial: m, l, pad, pad, o[64]
+constexpr int MAX_CLUSTER = 16;
+constexpr float kLog2eD = 1.4426950408889634f;
+
+template <int R>
+struct DecSmem {
+  float x[R][kD];                  // residual stream (replicated in every CTA)
+  float att[R][kD];                // combined attention output (local)
+  float melprev[R][kMelPad];       // previous frame, zero padded to 128 (broadcast target)
+  float bufA[R][LDA];              // broadcast targets, ping-pong
+  float bufB[R][LDA];
+  float part[MAX_CLUSTER / 4][kH][R][PSTRIDE];   // attention partials [split][head][row]
+  float wpart[DEC_WARPS][PSTRIDE]; // per-warp partials before the in-CTA combine
+  int exit_flag;
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y), c = unpack_bf16(u.z), d = unpack_bf16(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+
+// y[r][n] = sum_k in[r][k] * W[n][k] + bias[n] for n in [n_begin, n_end): one warp per output,
+// U outputs in flight per warp, lanes stride K in 16-byte weight loads.  emit(n, r, value) is called
+// by all 32 lanes with the reduced value.
+template <int R, int U, class Emit>
+__device__ __forceinline__ void gemv_slice(const bf16* __restrict__ W, int ldw, const float* __restrict__ bias, int K,
+                                           int n_begin, int n_end, const float* in, int ld_in, Emit&& emit) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int nb = n_begin + warp * U; nb < n_end; nb += DEC_WARPS * U) {
+    float acc[U][R];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int r = 0; r < R; ++r) acc[u][r] = 0.f;
+    for (int k0 = lane * 8; k0 < K; k0 += 256) {
+      uint4 w[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int n = nb + u;
+        w[u] = n < n_end ? __ldg(reinterpret_cast<const uint4*>(W + (size_t)n * ldw + k0)) : make_uint4(0, 0, 0, 0);
+      }
+      float xin[R][8];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float4 a = *reinterpret_cast<const float4*>(in + r * ld_in + k0);
+        const float4 b = *reinterpret_cast<const float4*>(in + r * ld_in + k0 + 4);
+        xin[r][0] = a.x; xin[r][1] = a.y; xin[r][2] = a.z; xin[r][3] = a.w;
+        xin[r][4] = b.x; xin[r][5] = b.y; xin[r][6] = b.z; xin[r][7] = b.w;
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        float wf[8];
+        unpack8(w[u], wf);
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[u][r] = fmaf(wf[i], xin[r][i], acc[u][r]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int n = nb + u;
+      if (n < n_end) {                         // warp-uniform
+        const float bn = __ldg(bias + n);
+#pragma unroll
+        for (int r = 0; r < R; ++r) emit(n, r, warp_sum(acc[u][r]) + bn);
+      }
+    }
+  }
+}
+
+// x[r] = LayerNorm(x[r] + delta[r]) for the R rows, one warp per row (eps 1e-5, biased variance).
+template <int R>
+__device__ __forceinline__ void add_layernorm(float (*x)[kD], const float (*delta)[LDA], const float* __restrict__ g,
+                                              const float* __restrict__ b) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int r = warp; r < R; r += DEC_WARPS) {
+    float v[8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { v[i] = x[r][lane + 32 * i] + delta[r][lane + 32 * i]; s += v[i]; }
+    const float mean = warp_sum(s) * (1.f / kD);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { const float d = v[i] - mean; q += d * d; }
+    const float rstd = rsqrtf(warp_sum(q) * (1.f / kD) + 1e-5f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = lane + 32 * i;
+      x[r][c] = (v[i] - mean) * rstd * __ldg(g + c) + __ldg(b + c);
+    }
+  }
+  __syncthreads();
+}
+
+struct Partial {      // one 8-lane group's running softmax state over its keys (8 head dims per lane)
+  float m, l, o[8];
+};
+
+__device__ __forceinline__ void partial_update(Partial& p, float s, const float (&vf)[8]) {
+  const float mn = fmaxf(p.m, s);
+  const float corr = exp2f((p.m - mn) * kLog2eD);       // p.m == -inf -> 0
+  const float e = exp2f((s - mn) * kLog2eD);
+  p.l = p.l * corr + e;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) p.o[i] = p.o[i] * corr + e * vf[i];
+  p.m = mn;
+}
+
+// merge the state held by the lane `mask` away (same head-dim slice) into this lane's state
+__device__ __forceinline__ void partial_merge_xor(Partial& p, int mask) {
+  const float m2 = __shfl_xor_sync(0xffffffffu, p.m, mask);
+  const float l2 = __shfl_xor_sync(0xffffffffu, p.l, mask);
+  const float mn = fmaxf(p.m, m2);
+  const float c1 = p.m == -INFINITY ? 0.f : exp2f((p.m - mn) * kLog2eD);
+  const float c2 = m2 == -INFINITY ? 0.f : exp2f((m2 - mn) * kLog2eD);
+  p.l = p.l * c1 + l2 * c2;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float o2 = __shfl_xor_sync(0xffffffffu, p.o[i], mask);
+    p.o[i] = p.o[i] * c1 + o2 * c2;
+  }
+  p.m = mn;
+}
+
+// Attention of one (row, head) query over this warp's share of the cached keys.
+//   kv        : first key row of this utterance/layer, bf16 [n_keys][512] (K at +0, V at +256)
+//   q         : 64 fp32 query values (already scaled)
+//   unit/units: this warp's index / count among the warps sharing the (row, head) key range
+//   cur_k/v   : optional extra key held in shared memory (the step's own k, v; fp32, rounded to bf16 here
+//               so that it matches what later steps read back from the cache)
+__device__ __forceinline__ Partial attend_keys(const bf16* kv, int n_keys, const float* q, int head, int unit,
+                                               int units, const float* cur_k, const float* cur_v) {
+  const int lane = threadIdx.x & 31;
+  const int grp = lane >> 3, dl = lane & 7;
+  float qf[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) qf[i] = q[dl * 8 + i];
+  Partial p;
+  p.m = -INFINITY; p.l = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) p.o[i] = 0.f;
+  const bf16* base = kv + head * kDh + dl * 8;
+  const int n_groups = (n_keys + 3) >> 2;
+  for (int g4 = unit; g4 < n_groups; g4 += 2 * units) {
+    // two independent 4-key groups per iteration keep four 16-byte loads in flight per lane
+    const int j0 = g4 * 4 + grp, j1 = (g4 + units) * 4 + grp;
+    const bool ok0 = j0 < n_keys, ok1 = j1 < n_keys;
+    uint4 k0 = make_uint4(0, 0, 0, 0), v0 = k0, k1 = k0, v1 = k0;
+    if (ok0) { k0 = __ldcg(reinterpret_cast<const uint4*>(base + (size_t)j0 * 512));
+               v0 = __ldcg(reinterpret_cast<const uint4*>(base + (size_t)j0 * 512 + 256)); }
+    if (ok1) { k1 = __ldcg(reinterpret_cast<const uint4*>(base + (size_t)j1 * 512));
+               v1 = __ldcg(reinterpret_cast<const uint4*>(base + (size_t)j1 * 512 + 256)); }
+    float kf[8], vf[8];
+    unpack8(k0, kf);
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s = fmaf(qf[i], kf[i], s);
+    s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2); s += __shfl_xor_sync(0xffffffffu, s, 4);
+    unpack8(v0, vf);
+    if (ok0) partial_update(p, s, vf);
+    unpack8(k1, kf);
+    s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s = fmaf(qf[i], kf[i], s);
+    s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2); s += __shfl_xor_sync(0xffffffffu, s, 4);
+    unpack8(v1, vf);
+    if (ok1) partial_update(p, s, vf);
+  }
+  if (cur_k != nullptr && unit == 0) {
+    float kf[8], vf[8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      kf[i] = __bfloat162float(__float2bfloat16(cur_k[head * kDh + dl * 8 + i]));
+      vf[i] = __bfloat162float(__float2bfloat16(cur_v[head * kDh + dl * 8 + i]));
+      s = fmaf(qf[i], kf[i], s);
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2); s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (grp == 0) partial_update(p, s, vf);
+  }
+  partial_merge_xor(p, 8);
+  partial_merge_xor(p, 16);
+  return p;          // lanes 0..7 (and their mirrors) hold the warp's result for dims dl*8..dl*8+7
+}
+
+template <int R>
+__global__ void __launch_bounds__(DEC_THREADS, 1) decode_kernel(const DecodeArgs a) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const int C = (int)cluster.num_blocks();
+  const int rank = (int)cluster.block_rank();
+  extern __shared__ __align__(16) uint8_t dec_smem_raw[];
+  DecSmem<R>& sm = *reinterpret_cast<DecSmem<R>*>(dec_smem_raw);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row0 = (blockIdx.x / C) * R;
+  DecSmem<R>* peer = cluster.map_shared_rank(&sm, lane % C);     // lane p publishes into CTA p
+
+  // attention work split: CTA -> (head, key split); warp -> (row, sub-unit)
+  const int head = rank & 3, split = rank >> 2, n_split = C >> 2;
+  constexpr int WPR = DEC_WARPS / R;                             // warps per row
+  const int arow = warp % R, wi = warp / R;
+  const int unit = split * WPR + wi, units = n_split * WPR;
+
+  for (int i = tid; i < R * kMelPad; i += DEC_THREADS) (&sm.melprev[0][0])[i] = 0.f;
+  if (tid == 0) sm.exit_flag = 0;
+  cluster.sync();
+
+  auto slice = [&](int N, int& nb, int& ne) {
+    const int per = (N + C - 1) / C;
+    nb = rank * per;
+    ne = min(N, nb + per);
+  };
+  auto row_valid = [&](int r) { return row0 + r < a.B; };
+  auto row_b = [&](int r) { return min(row0 + r, a.B - 1); };
+
+  // ---- attention over cached keys for (arow, head); publishes the CTA's partial to every peer
+  auto attention_phase = [&](const bf16* kv, int n_keys, const float* q, const float* cur_k, const float* cur_v) {
+    Partial p = attend_keys(kv, n_keys, q, head, unit, units, cur_k, cur_v);
+    const int dl = lane & 7;
+    if (lane < 8) {
+      float* w = sm.wpart[warp];
+      if (lane == 0) { w[0] = p.m; w[1] = p.l; }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) w[4 + dl * 8 + i] = p.o[i];
+    }
+    __syncthreads();
+    if (warp < R) {                                              // wi == 0: combine the WPR warps of row `warp`
+      float m = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < WPR; ++i) m = fmaxf(m, sm.wpart[warp + R * i][0]);
+      float l = 0.f, o[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = 0.f;
+#pragma unroll
+      for (int i = 0; i < WPR; ++i) {
+        const float* w = sm.wpart[warp + R * i];
+        const float c = w[0] == -INFINITY ? 0.f : exp2f((w[0] - m) * kLog2eD);
+        l += w[1] * c;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += w[4 + dl * 8 + j] * c;
+      }
+      for (int p0 = 0; p0 < C; p0 += 4) {
+        const int pr = p0 + (lane >> 3);
+        if (pr < C) {
+          float* dst = cluster.map_shared_rank(&sm.part[split][head][warp][0], pr);
+          if (dl == 0) { dst[0] = m; dst[1] = l; }
+          *reinterpret_cast<float4*>(dst + 4 + dl * 8) = make_float4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<float4*>(dst + 8 + dl * 8) = make_float4(o[4], o[5], o[6], o[7]);
+        }
+      }
+    }
+    cluster.sync();
+    // every CTA combines the key splits of all heads: thread -> (head, dim)
+    {
+      const int hh = tid >> 6, d = tid & 63;
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        float m = -INFINITY;
+        for (int s = 0; s < n_split; ++s) m = fmaxf(m, sm.part[s][hh][r][0]);
+        float l = 0.f, o = 0.f;
+        for (int s = 0; s < n_split; ++s) {
+          const float* w = sm.part[s][hh][r];
+          const float c = w[0] == -INFINITY ? 0.f : exp2f((w[0] - m) * kLog2eD);
+          l += w[1] * c;
+          o += w[4 + d] * c;
+        }
+        sm.att[r][tid] = l > 0.f ? o / l : 0.f;
+      }
+    }
+    __syncthreads();
+  };
+
+  int first_open = 0;          // (thread 0 of rank 0) first step whose stop verdict is still unknown
+
+  for (int t = 0; t < a.Tmax; ++t) {
+    int nb, ne;
+    // ---- stop rule, evaluated one step late by one thread while the others start the prenet
+    if (rank == 0 && tid == 0 && t > 0) {
+      const int base = first_open;
+      const int n_chk = min(8, t - base);
+      int vals[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) vals[i] = i < n_chk ? __ldcg(a.stop_count + base + i) : 0;
+      bool stop = false;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (i >= n_chk) break;
+        const int v = vals[i];
+        if ((v >> 16) != a.B) break;                             // some cluster has not reported this step yet
+        if ((v & 0xffff) == a.B) { stop = true; break; }
+        first_open = base + i + 1;
+      }
+      if (stop)
+        for (int p = 0; p < C; ++p) *cluster.map_shared_rank(&sm.exit_flag, p) = 1;
+    }
+    // ---- decoder prenet (model/model.py:61-67): relu(W1 mel_prev + b1)
+    slice(kD, nb, ne);
+    gemv_slice<R, 2>(a.w_pre1, kMelPad, a.b_pre1, kMelPad, nb, ne, &sm.melprev[0][0], kMelPad,
+                     [&](int n, int r, float v) { if (lane < C) peer->bufA[r][n] = fmaxf(v, 0.f); });
+    cluster.sync();
+    if (sm.exit_flag) break;
+    // relu(W2 . + b2) + alpha * pe[t]   (model/model.py:95, 355-356)
+    gemv_slice<R, 2>(a.w_pre2, kD, a.b_pre2, kD, nb, ne, &sm.bufA[0][0], LDA, [&](int n, int r, float v) {
+      if (lane < C) peer->bufB[r][n] = fmaxf(v, 0.f) + a.alpha * __ldg(a.pe + (size_t)t * kD + n);
+    });
+    cluster.sync();
+    for (int i = tid; i < R * kD; i += DEC_THREADS) sm.x[i / kD][i % kD] = sm.bufB[i / kD][i % kD];
+    __syncthreads();
+
+#pragma unroll 1
+    for (int l = 0; l < 3; ++l) {
+      const DecLayerW& w = a.layer[l];
+      // ---- self-attention: in-proj, cache append
+      slice(3 * kD, nb, ne);
+      gemv_slice<R, 4>(w.w_qkv, kD, w.b_qkv, kD, nb, ne, &sm.x[0][0], kD, [&](int n, int r, float v) {
+        if (lane < C) peer->bufA[r][n] = v;
+        if (lane == 0 && n >= kD && row_valid(r))
+          a.self_kv[(((size_t)l * a.B + row0 + r) * a.Tmax + t) * 512 + (n - kD)] = __float2bfloat16(v);
+      });
+      cluster.sync();
+      attention_phase(a.self_kv + ((size_t)l * a.B + row_b(arow)) * a.Tmax * 512, t, &sm.bufA[arow][head * kDh],
+                      &sm.bufA[arow][kD], &sm.bufA[arow][2 * kD]);
+      slice(kD, nb, ne);
+      gemv_slice<R, 2>(w.w_so, kD, w.b_so, kD, nb, ne, &sm.att[0][0], kD,
+                       [&](int n, int r, float v) { if (lane < C) peer->bufB[r][n] = v; });
+      cluster.sync();
+      add_layernorm<R>(sm.x, sm.bufB, w.ln1_g, w.ln1_b);
+      // ---- cross-attention over the precomputed memory K/V (keys >= phoneme_len masked)
+      gemv_slice<R, 2>(w.w_cq, kD, w.b_cq, kD, nb, ne, &sm.x[0][0], kD,
+                       [&](int n, int r, float v) { if (lane < C) peer->bufA[r][n] = v; });
+      cluster.sync();
+      attention_phase(a.cross_kv + ((size_t)l * a.B + row_b(arow)) * a.Tp * 512, min(a.ph_len[row_b(arow)], a.Tp),
+                      &sm.bufA[arow][head * kDh], nullptr, nullptr);
+      gemv_slice<R, 2>(w.w_co, kD, w.b_co, kD, nb, ne, &sm.att[0][0], kD,
+                       [&](int n, int r, float v) { if (lane < C) peer->bufB[r][n] = v; });
+      cluster.sync();
+      add_layernorm<R>(sm.x, sm.bufB, w.ln2_g, w.ln2_b);
+      // ---- position-wise FFN
+      slice(kF, nb, ne);
+      gemv_slice<R, 4>(w.w_f1, kD, w.b_f1, kD, nb, ne, &sm.x[0][0], kD,
+                       [&](int n, int r, float v) { if (lane < C) peer->bufA[r][n] = fmaxf(v, 0.f); });
+      cluster.sync();
+      slice(kD, nb, ne);
+      gemv_slice<R, 2>(w.w_f2, kF, w.b_f2, kF, nb, ne, &sm.bufA[0][0], LDA,
+                       [&](int n, int r, float v) { if (lane < C) peer->bufB[r][n] = v; });
+      cluster.sync();
+      add_layernorm<R>(sm.x, sm.bufB, w.ln3_g, w.ln3_b);
+    }
+
+    // ---- mel + stop heads (model/model.py:376-380); the frame is fed back un-rounded
+    slice(kMel + 1, nb, ne);
+    int rep = 0, cnt = 0;
+    gemv_slice<R, 1>(a.w_head, kD, a.b_head, kD, nb, ne, &sm.x[0][0], kD, [&](int n, int r, float v) {
+      if (n < kMel) {
+        if (lane < C) peer->melprev[r][n] = v;
+        if (lane == 0 && row_valid(r)) a.mel_out[((size_t)(row0 + r) * a.Tmax + t) * kMel + n] = v;
+      } else if (row_valid(r)) {
+        if (lane == 0) a.stop_out[(size_t)(row0 + r) * a.Tmax + t] = v;
+        ++rep;
+        cnt += v >= a.stop_logit ? 1 : 0;
+      }
+    });
+    if (lane == 0 && rep > 0) atomicAdd(a.stop_count + t, (rep << 16) | cnt);
+    cluster.sync();
+  }
+  cluster.sync();
+}
+
+__global__ void decode_finalize(const int* stop_count, int Tmax, int B, int* n_frames) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  int n = Tmax;
+  for (int t = 0; t < Tmax; ++t) {
+    const int v = stop_count[t];
+    if ((v >> 16) == B && (v & 0xffff) == B) { n = t + 1; break; }
+  }
+  *n_frames = n;
+}
+
+template <int R>
+static const char* launch_r(const DecodeArgs& a, int C, cudaStream_t s) {
+  const int n_clusters = (a.B + R - 1) / R;
+  const size_t smem = sizeof(DecSmem<R>);
+  if (cudaFuncSetAttribute(decode_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+    return "cudaFuncSetAttribute(decode smem) failed";
+  if (C > 8 &&
+      cudaFuncSetAttribute(decode_kernel<R>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
+    return "cudaFuncSetAttribute(decode non-portable cluster) failed";
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(n_clusters * C);
+  cfg.blockDim = dim3(DEC_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, decode_kernel<R>, a) != cudaSuccess) return "decode kernel launch failed";
+  decode_finalize<<<1, 32, 0, s>>>(a.stop_count, a.Tmax, a.B, a.n_frames);
+  return cudaGetLastError() == cudaSuccess ? nullptr : "decode finalize launch failed";
+}
+
+const char* decode_launch(const DecodeArgs& a, int R, int C, cudaStream_t s) {
+  if (a.B <= 0 || a.Tmax <= 0 || a.Tp <= 0) return "decode: empty problem";
+  if (a.B > 65535) return "decode: batch too large for the stop counter";
+  if (C != 4 && C != 8 && C != 16) return "decode: cluster size must be 4, 8 or 16";
+  switch (R) {
+    case 1: return launch_r<1>(a, C, s);
+    case 2: return launch_r<2>(a, C, s);
+    case 4: return launch_r<4>(a, C, s);
+    case 8: return launch_r<8>(a, C, s);
+    default: return "decode: rows per cluster must be 1, 2, 4 or 8";
+  }
+}
+
+}  // namespace tts

@@ -1,0 +1,74 @@
+// Internal launch API between c_api.cu (orchestration) and the kernel translation units.
+// Not part of the C ABI (include/tts_b200.h is).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace tts {
+
+typedef __nv_bfloat16 bf16;
+
+// model constants (config.yaml:25-42 of the reference; the kernels are specialised to them)
+constexpr int kD = 256;      // d_model
+constexpr int kH = 4;        // heads
+constexpr int kDh = 64;      // head dim
+constexpr int kF = 1024;     // FFN dim
+constexpr int kMel = 80;     // mel bins
+constexpr int kMelPad = 128; // mel bins padded to two 64-wide k-blocks
+constexpr int kTaps = 5;     // conv kernel size
+constexpr int kPeMax = 5000; // model/model.py:76
+
+enum Act { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2 };
+
+// One dense contraction  out[row, n] = epi( sum_k A[row(+tap), k] * W[n, k] ).
+// A is a bf16 activation viewed as [B][T][C] (a plain matrix is B=1, T=M); the K loop runs over
+// `taps` row-shifted copies of A (conv1d as implicit GEMM; rows outside [0,T) of the same utterance
+// read as zero through TMA out-of-bounds fill) times `kc_per_tap` 64-wide channel blocks.
+// W is bf16 [N][taps*kc_per_tap*64], K-major.
+struct GemmArgs {
+  const bf16* A;  int B, T, C;            // activation and its logical shape (C = true channels)
+  const bf16* W;  int N;                  // weight rows actually present in memory
+  int taps, tap_off, kc_per_tap;
+  // epilogue, applied in this order: +bias, act, +alpha*pe[t], +residual, LayerNorm, store
+  const float* bias;                      // [N]
+  int act;
+  const float* pe; float alpha; int pe_period;  // pe table [kPeMax][256] fp32 or null; position = row % pe_period
+  const bf16* residual; int ld_res;       // bf16 [B*T][ld_res] or null
+  const float* residual_f32; int ld_res32;// fp32 residual (PostNet tail) or null
+  const float* ln_g; const float* ln_b;   // LayerNorm over N == 256 or null
+  bf16* out_bf16; int ld_bf16;            // nullable
+  float* out_f32; int ld_f32;             // nullable
+  float* out_last;                        // if set, column N-1 goes to out_last[row] instead (stop head)
+};
+
+const char* gemm_launch(const GemmArgs& a, cudaStream_t s);   // returns nullptr or an error string
+
+// Fused masked-softmax attention over packed projections.
+// Q rows: q[(b*Tq + i)*ldq + h*64 + d], K/V likewise with Tk, ldk/ldv.  Keys j >= klen[b] are masked
+// when klen != nullptr; causal masks j > i.  Q is expected pre-scaled by 1/sqrt(64).
+// out[(b*Tq+i)*ldo + h*64 + d] bf16.  If probs != nullptr the normalised probabilities are stored as
+// fp32 [B][H][Tq][Tk] (model/layers.py:68-74).
+struct AttnArgs {
+  const bf16* Q; int ldq;
+  const bf16* K; int ldk;
+  const bf16* V; int ldv;
+  bf16* O; int ldo;
+  float* probs;
+  const int* klen;
+  int B, Tq, Tk, causal;
+};
+const char* attn_launch(const AttnArgs& a, cudaStream_t s);
+
+// small elementwise kernels
+const char* embed_launch(const int64_t* phoneme, const bf16* table, bf16* out, int n_tok, int n_phon,
+                         cudaStream_t s);
+const char* cast_mel_launch(const float* mel, bf16* out, size_t n, cudaStream_t s);
+const char* lens_launch(const int64_t* in, int* out, int n, int lo, int hi, cudaStream_t s);
+
+// tensor-map helper (driver entry point fetched through the runtime; no libcuda link dependency)
+const char* make_tmap_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
+                         uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1);
+
+}  // namespace tts
