@@ -1,0 +1,430 @@
+#!/usr/bin/env python
+"""bench.py -- mel frames/sec of the B200-native TransformerTTS hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload fwd|ar]
+
+A "step" is one teacher-forced forward (TransformerTTS.forward, model/model.py:260-320) over one batch of
+synthetic LJSpeech-shaped input; at N=1 the workload is BASELINE.json configs[1] (B=64, Tp=150, Tm=800,
+alignments returned).  With N>1 (torchrun, one rank per GPU) every rank runs the same per-GPU batch on its
+own utterances: weak scaling, no collective on the data path; the timing is the max over ranks.
+The line also carries AR-decode numbers (configs[2]), the roofline of the dominant kernel, the CPU baseline
+(the oracle port of the reference, timed on this box's host cores) and clocks sampled during the timed region.
+
+`--impl reference` times the reference's CPU implementation of the same path (the oracle port: the reference
+is pure PyTorch and /root/reference does not travel to the GPU box) with all host threads, rank 0 only.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+D, H, F, M, KS, L = 256, 4, 1024, 80, 5, 3
+CFG2 = dict(B=64, Tp=150, Tm=800)
+
+
+# ---------------------------------------------------------------------------------------------- helpers
+def algorithmic_flops(B, Tp, Tm, causal_skip=True):
+    """analytic FLOPs of one teacher-forced forward over the padded rectangle."""
+    Np, Nm = B * Tp, B * Tm
+    c = 0.5 if causal_skip else 1.0
+    enc_pre = Np * (3 * 2 * D * D * KS + 2 * D * D)
+    enc = Np * L * (8 * D * D + 4 * D * F + 4 * Tp * D)
+    dec_pre = Nm * (2 * M * D + 2 * D * D)
+    dec = Nm * L * (8 * D * D + 4 * D * D + 4 * D * F + c * 4 * Tm * D + 4 * Tp * D) + Np * L * 4 * D * D
+    heads = Nm * (2 * D * M + 2 * D)
+    post = Nm * (2 * 2 * M * D * KS + 3 * 2 * D * D * KS)
+    return float(enc_pre + enc + dec_pre + dec + heads + post)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm_gbs=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"],
+                    source="measured")
+    return dict(hbm_gbs=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = sorted(int(float(r[0])) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower() == "active" for r in self.rows)]
+        # median over the upper half = samples taken while the GPU was busy
+        busy = sm[len(sm) // 2:] if sm else []
+        return {"sm_mhz": busy[len(busy) // 2] if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------- CPU arm
+def _oracle():
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import tts_oracle as O          # checker / CPU baseline only; never on the product path
+    return O
+
+
+def cpu_forward_sample(B, Tp, Tm, reps, seed=1234):
+    """Times the oracle port of the reference forward on the host cores: B utterances of the cfg-2 lens law."""
+    import torch
+    O = _oracle()
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = O.make_state_dict(seed)
+    ph, mel, pl, ml = O.make_inputs(B, Tp, Tm, seed=seed + 1)
+    with torch.no_grad():
+        O.forward(sd, ph, mel, pl, ml)                       # warm-up (thread pool, allocator)
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            O.forward(sd, ph, mel, pl, ml)
+            ts.append(time.perf_counter() - t0)
+    ts.sort()
+    med = ts[len(ts) // 2]
+    return dict(seconds=med, valid_frames=int(ml.sum()), padded_frames=B * Tm, cores=torch.get_num_threads())
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port, all host threads), same metric/config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    B = 8                                                    # bounded sample of the cfg-2 batch (same lens law)
+    times, frames = [], 0
+    import torch
+    O = _oracle()
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = O.make_state_dict(1234)
+    ph, mel, pl, ml = O.make_inputs(B, CFG2["Tp"], CFG2["Tm"], seed=1235)
+    frames = int(ml.sum())
+    with torch.no_grad():
+        for _ in range(args.warmup):
+            O.forward(sd, ph, mel, pl, ml)
+        for _ in range(args.steps):
+            t0 = time.perf_counter()
+            O.forward(sd, ph, mel, pl, ml)
+            times.append(time.perf_counter() - t0)
+    ms = 1e3 * sum(times) / len(times)
+    value = frames / (ms / 1e3)
+    sample = f"{B} of the 64 utterances of configs[1] per step (same lens law), oracle port of the reference, fp32"
+    line = {
+        "impl": "reference", "metric": "mel frames/sec (teacher-forced forward)", "value": value,
+        "unit": "valid mel frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "configs[1]: teacher-forced forward, Tp=150, Tm=800, alignments returned",
+                   "sample_batch": B, "valid_frames_per_step": frames, "padded_frames_per_step": B * CFG2["Tm"]},
+        "cpu_baseline": {"value": value, "unit": "valid mel frames/s", "cores": torch.get_num_threads(),
+                         "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "valid mel frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------- GPU arm
+def make_batch(B, Tp, Tm, seed):
+    """Synthetic LJSpeech-shaped batch: lens ~ U[2/3 Tp, Tp] / U[5/8 Tm, Tm], rows sorted by
+    phoneme length descending (dataset.py:74-76), zero padding, mel ~ N(0,1)."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    pl = torch.randint(int(Tp * 2 / 3), Tp + 1, (B,), generator=g)
+    ml = torch.randint(int(Tm * 5 / 8), Tm + 1, (B,), generator=g)
+    pl[0] = Tp
+    ml[int(torch.randint(0, B, (1,), generator=g))] = Tm
+    pl, _ = torch.sort(pl, descending=True)
+    ph = torch.randint(1, 100, (B, Tp), generator=g) * (torch.arange(Tp)[None, :] < pl[:, None])
+    mel = torch.randn(B, Tm, M, generator=g) * (torch.arange(Tm)[None, :] < ml[:, None])[:, :, None]
+    return ph.long(), mel.float(), pl.long(), ml.long()
+
+
+class L2Flusher:
+    def __init__(self, dev):
+        import torch
+        self.buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # 256 MiB > 126 MB L2
+
+    def __call__(self):
+        self.buf.zero_()
+
+
+def time_kernel(fn, reps, flush):
+    """Average device time (ms) of one launch of fn(), events on the launching (current) stream."""
+    import torch
+    for _ in range(3):
+        fn()
+    tot = 0.0
+    for _ in range(reps):
+        flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record()
+        b.synchronize()
+        tot += a.elapsed_time(b)
+    return tot / reps
+
+
+def dominant_kernel_candidates(model, B, Tp, Tm, dev):
+    """The two kernel classes that carry the step: the tcgen05 GEMM (decoder FFN1 shape, the largest GEMM of
+    the step) and the fused causal self-attention.  Each entry: name, FLOPs per launch, launches of that
+    class per step, callable."""
+    import ctypes as C
+    import torch
+    from transformertts_b200 import _ext
+    lib = _ext.load()
+    Nm = B * Tm
+    st = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    A = torch.randn(Nm, D, device=dev).to(torch.bfloat16)
+    W = (torch.randn(F, D, device=dev) / 16).to(torch.bfloat16)
+    bias = torch.zeros(F, device=dev)
+    out = torch.empty(Nm, F, dtype=torch.bfloat16, device=dev)
+
+    def gemm():
+        _ext.check(lib.tts_op_linear(_ext.ptr(A), _ext.ptr(W), _ext.ptr(bias), Nm, F, D, 1, None, 0.0, 0, None, None,
+                                     None, _ext.ptr(out), None, st()), "tts_op_linear")
+
+    qkv = (torch.randn(B, Tm, 3 * D, device=dev) * 0.5).to(torch.bfloat16)
+    o = torch.empty(B, Tm, D, dtype=torch.bfloat16, device=dev)
+    klen = torch.full((B,), Tm, dtype=torch.int32, device=dev)
+    q, k, v = qkv[:, :, :D], qkv[:, :, D:2 * D], qkv[:, :, 2 * D:]
+
+    def attn():
+        _ext.check(lib.tts_op_attention(C.c_void_p(q.data_ptr()), 3 * D, C.c_void_p(k.data_ptr()), 3 * D,
+                                        C.c_void_p(v.data_ptr()), 3 * D, B, Tm, Tm, _ext.ptr(klen), 1, _ext.ptr(o),
+                                        None, st()), "tts_op_attention")
+
+    keep = (A, W, bias, out, qkv, o, klen)
+    return [
+        dict(name="gemm_kernel<256> decoder FFN1 (51200x1024x256, bias+ReLU)", flops=2.0 * Nm * F * D, per_step=3,
+             fn=gemm, keep=keep),
+        dict(name="attn_kernel decoder causal self-attention (B x 4 heads, 800x800x64, causal-skipped flops)",
+             flops=0.5 * 4.0 * Nm * Tm * D, per_step=3, fn=attn, keep=keep),
+    ]
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    from transformertts_b200 import TransformerTTS, _ext
+    lib = _ext.load()
+    torch.manual_seed(1234)
+    model = TransformerTTS(device=dev).eval()          # random init, reference init laws (model/module.py:21-25)
+    with torch.no_grad():
+        model.linear2.linear.bias.fill_(-1.0e4)        # never-stop bias for the AR throughput runs
+    model.refresh_weights()
+
+    B, Tp, Tm = CFG2["B"], CFG2["Tp"], CFG2["Tm"]
+    ph, mel, pl, ml = make_batch(B, Tp, Tm, seed=1 + rank)            # each rank: its own 64 utterances
+    valid, padded = int(ml.sum()), B * Tm
+    hph, hmel, hpl, hml = (t.pin_memory() for t in (ph, mel, pl, ml))
+    dph, dmel, dpl, dml = (t.to(dev) for t in (ph, mel, pl, ml))
+    flush = L2Flusher(dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---- device-resident forward: the headline `value`
+    for _ in range(max(args.warmup, 3)):
+        out = model(dph, dmel, dpl, dml)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n0 = lib.tts_launch_count()
+    step_ms = []
+    for _ in range(args.steps):
+        flush()                                        # L2 flush between timed iterations (outside the events)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = model(dph, dmel, dpl, dml)
+        b.record()
+        b.synchronize()
+        step_ms.append(a.elapsed_time(b))
+    launches = int(lib.tts_launch_count() - n0)
+    barrier()
+    ms_step = max_over_ranks(sum(step_ms) / len(step_ms))
+    total_valid = sum_over_ranks(valid)
+    total_padded = padded * world
+    value = total_valid / (ms_step / 1e3)
+
+    # ---- end to end through the public API with host buffers (pinned H2D in, D2H of the mel/stop result out)
+    hout = {k: torch.empty_like(out[k], device="cpu").pin_memory() for k in ("pred_melspec", "post_melspec", "pred_stop")}
+    h2d = sum(t.numel() * t.element_size() for t in (hph, hmel, hpl, hml))
+    d2h = sum(t.numel() * t.element_size() for t in hout.values())
+
+    def e2e_step():
+        o = model(hph.to(dev, non_blocking=True), hmel.to(dev, non_blocking=True), hpl.to(dev, non_blocking=True),
+                  hml.to(dev, non_blocking=True))
+        for k, t in hout.items():
+            t.copy_(o[k], non_blocking=True)
+        torch.cuda.synchronize()
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    barrier()
+    e2e_s = max_over_ranks(e2e_s)
+    clocks = sampler.stop() if rank == 0 else None
+    e2e_value = total_valid / e2e_s
+
+    # ---- AR decode (configs[2]): B=1 and B=32, Tp=150, 1000 frames, never-stop bias; whole inference() call
+    ar = {}
+    if not args.no_ar:
+        for Bar in (1, 32):
+            aph, _, apl, _ = make_batch(Bar, Tp, 8, seed=100 + rank)
+            aph, apl = aph.to(dev), apl.to(dev)
+            model.inference(aph, apl, max_len=1001)
+            torch.cuda.synchronize()
+            ts = []
+            for _ in range(3):
+                flush()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                r = model.inference(aph, apl, max_len=1001)
+                b.record()
+                b.synchronize()
+                ts.append(a.elapsed_time(b))
+            ts.sort()
+            T = r["pred_melspec"].shape[1]
+            ms = max_over_ranks(ts[1])
+            # algorithmic bytes: self-KV reads sum_t B*L*2*t*d*2 + cross-KV reads + weights once per step
+            kv = Bar * L * 2 * D * 2 * (T * (T - 1) / 2) + T * Bar * L * 2 * Tp * D * 2
+            wbytes = T * 5.75e6
+            ar[f"B{Bar}"] = {"frames_per_s": world * Bar * T / (ms / 1e3), "ms_total": ms, "frames": T,
+                             "us_per_step": 1e3 * ms / T,
+                             "achieved_gbs": (kv + wbytes) / (ms / 1e3) / 1e9}
+
+    # ---- roofline of the dominant kernel, timed alone on this stream (burst peak)
+    peaks = measured_peaks()
+    roofline, kernels = None, []
+    if rank == 0:
+        for c in dominant_kernel_candidates(model, B, Tp, Tm, dev):
+            ms = time_kernel(c["fn"], 10, flush)
+            kernels.append({"name": c["name"], "ms_per_launch": ms, "tflops": c["flops"] / (ms / 1e3) / 1e12,
+                            "launches_per_step": c["per_step"], "share_of_step": c["per_step"] * ms / ms_step})
+        top = max(kernels, key=lambda k: k["share_of_step"])
+        roofline = {"bound": "tensor", "kernel": top["name"], "achieved": top["tflops"], "peak": peaks["tf_burst"],
+                    "unit": "TFLOP/s", "frac": top["tflops"] / peaks["tf_burst"], "traffic": None,
+                    "peak_source": peaks["source"] + " (burst: kernel timed alone)"}
+    fl = algorithmic_flops(B, Tp, Tm, True) * world
+    step_roofline = {"flops_causal_skipped": fl, "achieved_tflops": fl / (ms_step / 1e3) / 1e12,
+                     "peak_tflops_sustained": peaks["tf_sustained"] * world,
+                     "frac": fl / (ms_step / 1e3) / 1e12 / (peaks["tf_sustained"] * world),
+                     "align_store_bytes": 3 * B * H * Tm * Tp * 4 * world}
+
+    # ---- CPU baseline on this box's host cores (rank 0, N=1 only): bounded sample of the same workload
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        s = cpu_forward_sample(8, Tp, Tm, reps=3)
+        cpu = {"value": s["valid_frames"] / s["seconds"], "unit": "valid mel frames/s", "cores": s["cores"],
+               "kind": "port",
+               "sample": f"8 of the 64 utterances of configs[1] (same lens law), median of 3 after 1 warm-up, "
+                         f"{s['seconds']:.2f} s per forward, oracle port of the reference in fp32 torch"}
+
+    if rank == 0:
+        line = {
+            "metric": "mel frames/sec (teacher-forced forward)", "value": value, "unit": "valid mel frames/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "configs[1]: teacher-forced forward, B=64 per GPU, Tp=150, Tm=800, alignments "
+                                   "returned (3x[B,4,Tm,Tp] fp32)",
+                       "batch_per_gpu": B, "valid_frames_per_step": total_valid, "padded_frames_per_step": total_padded,
+                       "padded_frames_per_s": total_padded / (ms_step / 1e3), "parallelism": f"batch-sharded x{world}, no collective",
+                       "l2": "256 MiB buffer written between timed iterations; working set (475 MB) also exceeds L2",
+                       "weights": "random init (reference init laws), bf16"},
+            "e2e": {"value": e2e_value, "unit": "valid mel frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_s * 1e3,
+                    "note": "pinned host inputs -> forward -> pred/post/stop copied to pinned host; alignments stay on "
+                            "the device as in the reference (utils/plot.py copies single maps)"},
+            "gpu_launches": launches,
+            "roofline": roofline, "kernels": kernels, "step_roofline": step_roofline,
+            "ar_decode": ar, "cpu_baseline": cpu, "clocks": clocks,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-ar", action="store_true", help="skip the AR-decode section")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

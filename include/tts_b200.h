@@ -72,6 +72,8 @@ typedef struct TtsWeights {
 
 int tts_abi_version(void);
 const char* tts_last_error(void);
+/* Number of CUDA kernels this library has launched in this process so far (monotonic). */
+uint64_t tts_launch_count(void);
 
 /* Bytes of scratch the calls below need for these sizes (Tm = frames; for tts_decode pass max frames). */
 size_t tts_workspace_bytes(int B, int Tp, int Tm);

@@ -50,6 +50,7 @@ class Weights(C.Structure):
 SIGNATURES = {
     "tts_abi_version": (C.c_int, []),
     "tts_last_error": (C.c_char_p, []),
+    "tts_launch_count": (C.c_uint64, []),
     "tts_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "tts_forward": (C.c_int, [C.POINTER(Weights), vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int,
                               vp, vp, vp, vp, vp, C.c_size_t, vp]),

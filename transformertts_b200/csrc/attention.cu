@@ -262,6 +262,7 @@ const char* attn_launch(const AttnArgs& a, cudaStream_t s) {
   }
   dim3 grid((a.Tq + AQ - 1) / AQ, kH, a.B);
   attn_kernel<<<grid, ATT_THREADS, sizeof(AttnSmem), s>>>(a);
+  note_launch();
   return cudaGetLastError() == cudaSuccess ? nullptr : "attention kernel launch failed";
 }
 

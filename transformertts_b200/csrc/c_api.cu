@@ -25,7 +25,11 @@ static int fail(const char* msg) {
   } while (0)
 
 // ------------------------------------------------------------------ small kernels
+#include <atomic>
+static std::atomic<unsigned long long> g_launches{0};
 namespace tts {
+
+void note_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 __global__ void embed_kernel(const int64_t* __restrict__ ph, const uint4* __restrict__ table, uint4* __restrict__ out,
                              int n_tok, int n_phon) {
@@ -63,15 +67,18 @@ const char* embed_launch(const int64_t* phoneme, const bf16* table, bf16* out, i
   const int n = n_tok * 32;
   embed_kernel<<<(n + 255) / 256, 256, 0, s>>>(phoneme, reinterpret_cast<const uint4*>(table),
                                                 reinterpret_cast<uint4*>(out), n_tok, n_phon);
+  note_launch();
   return cudaGetLastError() == cudaSuccess ? nullptr : "embedding kernel launch failed";
 }
 const char* cast_mel_launch(const float* mel, bf16* out, size_t n, cudaStream_t s) {
   const size_t thr = (n + 3) / 4;
   cast_mel_kernel<<<(unsigned)((thr + 255) / 256), 256, 0, s>>>(mel, out, n);
+  note_launch();
   return cudaGetLastError() == cudaSuccess ? nullptr : "cast kernel launch failed";
 }
 const char* lens_launch(const int64_t* in, int* out, int n, int lo, int hi, cudaStream_t s) {
   lens_kernel<<<(n + 127) / 128, 128, 0, s>>>(in, out, n, lo, hi);
+  note_launch();
   return cudaGetLastError() == cudaSuccess ? nullptr : "lens kernel launch failed";
 }
 
@@ -141,6 +148,7 @@ static Workspace carve(void* base, int B, int Tp, int Tm) {
 
 extern "C" int tts_abi_version(void) { return TTS_ABI_VERSION; }
 extern "C" const char* tts_last_error(void) { return g_err; }
+extern "C" uint64_t tts_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 extern "C" size_t tts_workspace_bytes(int B, int Tp, int Tm) {
   if (B <= 0 || Tp <= 0 || Tm < 0) return 0;
   return carve(nullptr, B, Tp, Tm).total;

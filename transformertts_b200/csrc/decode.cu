@@ -426,6 +426,7 @@ static const char* launch_r(const DecodeArgs& a, int C, cudaStream_t s) {
   cfg.attrs = attr; cfg.numAttrs = 1;
   if (cudaLaunchKernelEx(&cfg, decode_kernel<R>, a) != cudaSuccess) return "decode kernel launch failed";
   decode_finalize<<<1, 32, 0, s>>>(a.stop_count, a.Tmax, a.B, a.n_frames);
+  note_launch(2);
   return cudaGetLastError() == cudaSuccess ? nullptr : "decode finalize launch failed";
 }
 

@@ -32,6 +32,7 @@ struct GemmDev {
   bf16* out_bf16; int ld_bf16;
   float* out_f32; int ld_f32;
   float* out_last;
+  int vec16, vec32;                 // row pitches / bases allow 16-byte stores
 };
 
 template <int BN, int ST>
@@ -110,7 +111,7 @@ __device__ __forceinline__ void epi_store(const GemmDev& p, int n0, int c, size_
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       const int cg = col0 + g * 8;
-      if (cg + 8 <= n_main) {
+      if (p.vec16 && cg + 8 <= n_main) {
         uint4 u;
         u.x = pack_bf16(v[g * 8 + 0], v[g * 8 + 1]); u.y = pack_bf16(v[g * 8 + 2], v[g * 8 + 3]);
         u.z = pack_bf16(v[g * 8 + 4], v[g * 8 + 5]); u.w = pack_bf16(v[g * 8 + 6], v[g * 8 + 7]);
@@ -127,7 +128,7 @@ __device__ __forceinline__ void epi_store(const GemmDev& p, int n0, int c, size_
 #pragma unroll
     for (int g = 0; g < 8; ++g) {
       const int cg = col0 + g * 4;
-      if (cg + 4 <= n_main) {
+      if (p.vec32 && cg + 4 <= n_main) {
         *reinterpret_cast<float4*>(o + g * 4) = make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
       } else {
 #pragma unroll
@@ -314,6 +315,7 @@ static const char* launch_t(const CUtensorMap& tmA, const CUtensorMap& tmW, cons
     attr_done = true;
   }
   gemm_kernel<BN, ST><<<grid, GEMM_THREADS, S::TOTAL, s>>>(tmA, tmW, p);
+  note_launch();
   return cudaGetLastError() == cudaSuccess ? nullptr : "gemm kernel launch failed";
 }
 
@@ -337,6 +339,12 @@ const char* gemm_launch(const GemmArgs& a, cudaStream_t s) {
   p.out_bf16 = a.out_bf16; p.ld_bf16 = a.ld_bf16;
   p.out_f32 = a.out_f32; p.ld_f32 = a.ld_f32;
   p.out_last = a.out_last;
+  p.vec16 = a.out_bf16 != nullptr && a.ld_bf16 % 8 == 0 && (reinterpret_cast<uintptr_t>(a.out_bf16) & 15) == 0;
+  p.vec32 = a.out_f32 != nullptr && a.ld_f32 % 4 == 0 && (reinterpret_cast<uintptr_t>(a.out_f32) & 15) == 0;
+  if (a.residual != nullptr && (a.ld_res % 8 != 0 || (reinterpret_cast<uintptr_t>(a.residual) & 15) != 0))
+    return "gemm: bf16 residual must be 16-byte aligned with a row pitch that is a multiple of 8";
+  if ((reinterpret_cast<uintptr_t>(a.A) & 15) != 0 || (reinterpret_cast<uintptr_t>(a.W) & 15) != 0)
+    return "gemm: operands must be 16-byte aligned";
   const bool wide = ln || (a.N % 256 == 0);
   const int BN = wide ? 256 : 128;
   p.n_tiles = (a.N + BN - 1) / BN;

@@ -20,6 +20,8 @@ constexpr int kMelPad = 128; // mel bins padded to two 64-wide k-blocks
 constexpr int kTaps = 5;     // conv kernel size
 constexpr int kPeMax = 5000; // model/model.py:76
 
+void note_launch(int n = 1);      // counts kernel launches (tts_launch_count in the C ABI)
+
 enum Act { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2 };
 
 // One dense contraction  out[row, n] = epi( sum_k A[row(+tap), k] * W[n, k] ).
