@@ -41,29 +41,31 @@ struct GemmSmem {
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_OFF = ST * STAGE_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;  // barriers + manual 1024 B alignment slack
+  static constexpr int PAR_OFF = BAR_OFF + 256;       // bias | ln_g | ln_b, BN floats each
+  static constexpr int TOTAL = PAR_OFF + 3 * BN * 4 + 1024;  // + manual 1024 B alignment slack
 };
 
 // Loads accumulator chunk `c` (32 columns) of this thread's row and applies bias/act/PE/residual.
 template <int BN>
-__device__ __forceinline__ void epi_chunk(const GemmDev& p, uint32_t taddr, int c, int n0, bool valid,
-                                          size_t grow, int t_pe, float (&v)[32]) {
+__device__ __forceinline__ void epi_chunk(const GemmDev& p, const float* s_bias, uint32_t taddr, int c, int n0,
+                                          bool valid, size_t grow, int t_pe, float (&v)[32]) {
   uint32_t r[32];
   tmem_ld32(taddr + c * 32, r);
   tmem_ld_wait();
   const int col0 = n0 + c * 32;
+  const float4* sb = reinterpret_cast<const float4*>(s_bias + c * 32);   // zero beyond N (W rows there are zero too)
 #pragma unroll
-  for (int j = 0; j < 32; ++j) {
-    const int col = col0 + j;
-    float x = __uint_as_float(r[j]);
-    if (col < p.N) {
-      x += __ldg(p.bias + col);
-      if (p.act == ACT_RELU) x = fmaxf(x, 0.f);
-      else if (p.act == ACT_TANH) x = tanhf(x);
-    } else {
-      x = 0.f;
-    }
-    v[j] = x;
+  for (int j = 0; j < 8; ++j) {
+    const float4 b4 = sb[j];
+    v[j * 4 + 0] = __uint_as_float(r[j * 4 + 0]) + b4.x; v[j * 4 + 1] = __uint_as_float(r[j * 4 + 1]) + b4.y;
+    v[j * 4 + 2] = __uint_as_float(r[j * 4 + 2]) + b4.z; v[j * 4 + 3] = __uint_as_float(r[j * 4 + 3]) + b4.w;
+  }
+  if (p.act == ACT_RELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+  } else if (p.act == ACT_TANH) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = tanhf(v[j]);
   }
   if (!valid) return;
   if (p.pe != nullptr) {
@@ -149,6 +151,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* empty = full + ST;
   uint64_t* accum_full = empty + ST;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_full + 1);
+  float* s_bias = reinterpret_cast<float*>(smem + S::PAR_OFF);
+  float* s_lng = s_bias + BN;
+  float* s_lnb = s_lng + BN;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -220,6 +225,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const size_t grow = (size_t)b * p.T + (valid ? t : 0);
     const int t_pe = p.pe_period > 0 ? (int)(grow % (size_t)p.pe_period) : 0;
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    // stage the per-column epilogue vectors once per CTA while the mainloop runs
+    for (int i = threadIdx.x - 64; i < BN; i += 128) {
+      const int col = n0 + i;
+      const bool in = col < p.N;
+      s_bias[i] = in ? __ldg(p.bias + col) : 0.f;
+      if (p.ln_g != nullptr) { s_lng[i] = in ? __ldg(p.ln_g + col) : 0.f; s_lnb[i] = in ? __ldg(p.ln_b + col) : 0.f; }
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
     mbar_wait(accum_full, 0);
     tc_fence_after();
     float v[32];
@@ -227,7 +240,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       float sum = 0.f, sq = 0.f;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
-        epi_chunk<BN>(p, taddr, c, n0, valid, grow, t_pe, v);
+        epi_chunk<BN>(p, s_bias, taddr, c, n0, valid, grow, t_pe, v);
 #pragma unroll
         for (int j = 0; j < 32; ++j) { sum += v[j]; sq += v[j] * v[j]; }
       }
@@ -236,19 +249,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const float rstd = rsqrtf(var + 1e-5f);
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
-        epi_chunk<BN>(p, taddr, c, n0, valid, grow, t_pe, v);
+        epi_chunk<BN>(p, s_bias, taddr, c, n0, valid, grow, t_pe, v);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int col = n0 + c * 32 + j;
-          v[j] = (v[j] - mean) * rstd * __ldg(p.ln_g + col) + __ldg(p.ln_b + col);
-        }
+        for (int j = 0; j < 32; ++j)
+          v[j] = (v[j] - mean) * rstd * s_lng[c * 32 + j] + s_lnb[c * 32 + j];
         if (valid) epi_store(p, n0, c, grow, v);
       }
     } else {
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         if (n0 + c * 32 >= p.N) break;            // warp-uniform
-        epi_chunk<BN>(p, taddr, c, n0, valid, grow, t_pe, v);
+        epi_chunk<BN>(p, s_bias, taddr, c, n0, valid, grow, t_pe, v);
         if (valid) epi_store(p, n0, c, grow, v);
       }
     }
