@@ -10,6 +10,8 @@
 // ConvNormBN (model/module.py:18-19,28-33; BN folded on the host), MultiheadAttention in/out projections
 // (torch/nn/functional.py:5798,6665), FFN linear1/linear2 and the post-norm residual+LayerNorm
 // (torch/nn/modules/transformer.py:951-982), PositionalEncoding add (model/model.py:95).
+#include <stdlib.h>
+
 #include "kernels.h"
 #include "ptx.cuh"
 
@@ -336,6 +338,10 @@ const char* gemm_launch(const GemmArgs& a, cudaStream_t s) {
   const bool ln = a.ln_g != nullptr;
   if (ln && a.N != 256) return "gemm: LayerNorm epilogue needs N == 256";
   if (a.pe != nullptr && (a.N != kD || a.pe_period <= 0)) return "gemm: PE epilogue needs N == 256 and a period";
+  {
+    static const bool force_v1 = getenv("TTS_GEMM_V1") != nullptr;
+    if (!force_v1 && gemm2_supports(a)) return gemm2_launch(a, s);
+  }
   const int ktot = a.taps * a.kc_per_tap * BK;
   GemmDev p;
   p.B = a.B; p.T = a.T; p.N = a.N;

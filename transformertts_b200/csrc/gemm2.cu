@@ -1,0 +1,339 @@
+// Persistent tcgen05 / TMEM / TMA contraction, bf16 in -> bf16 out, N a multiple of 256 (sm_100a).
+//
+// The workhorse of the teacher-forced forward: QKV / out / FFN projections, the conv1d layers as implicit
+// GEMM (tap-shifted TMA windows) and the post-norm residual + LayerNorm blocks.  One CTA per SM walks the
+// (m, n) tile list with a fixed stride.  Roles:
+//   warp 0      TMA producer  : A 128x64 and W 256x64 k-blocks (SWIZZLE_128B) into a 3-stage ring
+//   warp 1      MMA issuer    : one thread, tcgen05.mma.cta_group::1.kind::f16 128x256x16, fp32 accumulators in
+//                               TMEM, two 256-column buffers so tile i+1 is multiplied while tile i drains
+//   warps 2..5  epilogue      : tcgen05.ld (thread == output row) -> +bias -> ReLU/tanh -> +alpha*PE ->
+//                               [+residual -> LayerNorm(256) with the pre-norm row parked back in TMEM] ->
+//                               bf16 -> 128B-swizzled shared slabs -> TMA tensor store (coalesced, async)
+// The residual tile arrives by TMA into the same slabs the result leaves from (in-place per thread).
+//
+// Replaces: nn.Linear / LinearNorm (model/module.py:36-53), Conv1d+BatchNorm1d of ConvNormBN
+// (model/module.py:18-19,28-33, BN folded), MultiheadAttention in/out projections (torch/nn/functional.py:5798,6665),
+// FFN + residual + LayerNorm (torch/nn/modules/transformer.py:951-982), PositionalEncoding (model/model.py:95).
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace tts {
+
+namespace g2 {
+constexpr int BM = 128, BN = 256, BK = 64, ST = 3;
+constexpr int THREADS = 192;
+constexpr int A_BYTES = BM * BK * 2;               // 16 KB
+constexpr int B_BYTES = BN * BK * 2;               // 32 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;     // 48 KB
+constexpr int SLAB_BYTES = BM * 64 * 2;            // 128 rows x 64 bf16 columns = 16 KB
+constexpr int SLAB_OFF = ST * STAGE_BYTES;         // 144 KB
+constexpr int BAR_OFF = SLAB_OFF + 4 * SLAB_BYTES; // 208 KB
+constexpr int PAR_OFF = BAR_OFF + 256;
+constexpr int MAX_N = 1024;
+constexpr int TOTAL = PAR_OFF + (MAX_N + 2 * BN) * 4 + 1024;
+
+struct Dev {
+  int T, N;
+  int tap_off, kc_per_tap, num_kb;
+  int tiles_per_utt, n_tiles, total_tiles;
+  const float* bias;
+  int act;
+  const float* pe; float alpha; int pe_period;
+  const float* ln_g; const float* ln_b;
+  int has_res;
+};
+}  // namespace g2
+
+using namespace g2;
+
+template <bool LN>
+__global__ void __launch_bounds__(THREADS, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const Dev p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
+  uint64_t* empty = full + ST;
+  uint64_t* acc_full = empty + ST;      // [2]
+  uint64_t* acc_empty = acc_full + 2;   // [2]
+  uint64_t* res_full = acc_empty + 2;   // [4]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 4);
+  float* s_bias = reinterpret_cast<float*>(smem + PAR_OFF);   // [MAX_N]
+  float* s_lng = s_bias + MAX_N;                              // [256]
+  float* s_lnb = s_lng + BN;                                  // [256]
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmO);
+    if (LN) tma_prefetch_desc(&tmR);
+    for (int s = 0; s < ST; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, 4); }
+    for (int i = 0; i < 4; ++i) mbar_init(res_full + i, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  if (warp >= 2) {
+    for (int i = threadIdx.x - 64; i < p.N; i += 128) s_bias[i] = __ldg(p.bias + i);
+    if (LN)
+      for (int i = threadIdx.x - 64; i < BN; i += 128) { s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+        const int b = m_tile / p.tiles_per_utt, t0 = (m_tile % p.tiles_per_utt) * BM, n0 = n_tile * BN;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          const int tap = kb / p.kc_per_tap;
+          const int kc = kb - tap * p.kc_per_tap;
+          mbar_wait(empty + s, ph ^ 1);
+          mbar_expect_tx(full + s, STAGE_BYTES);
+          uint8_t* sa = smem + s * STAGE_BYTES;
+          tma_load_3d(sa, &tmA, full + s, kc * BK, t0 + tap + p.tap_off, b);
+          tma_load_3d(sa + A_BYTES, &tmW, full + s, kb * BK, n0, 0);
+          if (++s == ST) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      int s = 0; uint32_t ph = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const uint32_t use = static_cast<uint32_t>(it >> 1);
+        mbar_wait(acc_empty + buf, (use & 1) ^ 1);           // epilogue has drained this TMEM buffer
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + buf * BN;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(full + s, ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+          const uint64_t da = umma_desc_sw128(sa);
+          const uint64_t db = umma_desc_sw128(sa + A_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            tc_mma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          tc_commit(empty + s);
+          if (kb == p.num_kb - 1) tc_commit(acc_full + buf);
+          if (++s == ST) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------ epilogue: thread == output row
+    const int q = warp & 3;                        // TMEM lane quadrant of this warp
+    const int row = q * 32 + lane;
+    const bool leader = threadIdx.x == 64;
+    uint8_t* slabs = smem + SLAB_OFF;
+    const uint32_t sw = static_cast<uint32_t>(row & 7);
+    uint8_t* my_row = slabs + row * 128;           // + slab * SLAB_BYTES + ((chunk16 ^ sw) << 4)
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+      const int b = m_tile / p.tiles_per_utt, t0 = (m_tile % p.tiles_per_utt) * BM, n0 = n_tile * BN;
+      const int buf = it & 1;
+      const uint32_t use = static_cast<uint32_t>(it >> 1);
+      const uint32_t tacc = tmem_base + buf * BN + (static_cast<uint32_t>(q * 32) << 16);
+      if (LN && leader) {
+        bulk_wait_read<0>();                       // the previous tile's stores have left the slabs
+        for (int s = 0; s < 4; ++s) {
+          mbar_expect_tx(res_full + s, SLAB_BYTES);
+          tma_load_3d(slabs + s * SLAB_BYTES, &tmR, res_full + s, s * 64, t0, b);
+        }
+      }
+      mbar_wait(acc_full + buf, use & 1);
+      tc_fence_after();
+
+      float mean = 0.f, rstd = 1.f;
+      if (LN) {
+        // pass 1: v = acc + bias + residual; row statistics; v parked back in TMEM
+        float sum = 0.f, sq = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 8; ++c) {
+          uint32_t r[32];
+          tmem_ld32(tacc + c * 32, r);
+          if ((c & 1) == 0) mbar_wait(res_full + (c >> 1), it & 1);
+          const uint8_t* rs = my_row + (c >> 1) * SLAB_BYTES;
+          uint4 res[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            res[j] = *reinterpret_cast<const uint4*>(rs + ((static_cast<uint32_t>((c & 1) * 4 + j) ^ sw) << 4));
+          tmem_ld_wait();
+          const float4* sb = reinterpret_cast<const float4*>(s_bias + c * 32);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 b0 = sb[2 * j], b1 = sb[2 * j + 1];
+            const float2 x0 = unpack_bf16(res[j].x), x1 = unpack_bf16(res[j].y), x2 = unpack_bf16(res[j].z),
+                         x3 = unpack_bf16(res[j].w);
+            float v[8];
+            v[0] = __uint_as_float(r[j * 8 + 0]) + b0.x + x0.x; v[1] = __uint_as_float(r[j * 8 + 1]) + b0.y + x0.y;
+            v[2] = __uint_as_float(r[j * 8 + 2]) + b0.z + x1.x; v[3] = __uint_as_float(r[j * 8 + 3]) + b0.w + x1.y;
+            v[4] = __uint_as_float(r[j * 8 + 4]) + b1.x + x2.x; v[5] = __uint_as_float(r[j * 8 + 5]) + b1.y + x2.y;
+            v[6] = __uint_as_float(r[j * 8 + 6]) + b1.z + x3.x; v[7] = __uint_as_float(r[j * 8 + 7]) + b1.w + x3.y;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { sum += v[e]; sq += v[e] * v[e]; r[j * 8 + e] = __float_as_uint(v[e]); }
+          }
+          tmem_st32(tacc + c * 32, r);
+        }
+        tmem_st_wait();
+        mean = sum * (1.f / BN);
+        rstd = rsqrtf(fmaxf(sq * (1.f / BN) - mean * mean, 0.f) + 1e-5f);
+      }
+
+      const int t_row = t0 + row;
+      const int t_pe = p.pe != nullptr ? ((b * p.T + min(t_row, p.T - 1)) % p.pe_period) : 0;
+#pragma unroll 1
+      for (int c = 0; c < 8; ++c) {
+        uint32_t r[32];
+        tmem_ld32(tacc + c * 32, r);
+        float v[32];
+        if (!LN && p.pe != nullptr) {
+          const float4* pr = reinterpret_cast<const float4*>(p.pe + (size_t)t_pe * kD + n0 + c * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 q4 = __ldg(pr + j);
+            v[j * 4 + 0] = p.alpha * q4.x; v[j * 4 + 1] = p.alpha * q4.y;
+            v[j * 4 + 2] = p.alpha * q4.z; v[j * 4 + 3] = p.alpha * q4.w;
+          }
+        }
+        tmem_ld_wait();
+        if (c == 7) {                               // last read of this TMEM buffer: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acc_empty + buf);
+        }
+        if (LN) {
+          const float4* g4 = reinterpret_cast<const float4*>(s_lng + c * 32);
+          const float4* b4 = reinterpret_cast<const float4*>(s_lnb + c * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 g = g4[j], bb = b4[j];
+            v[j * 4 + 0] = (__uint_as_float(r[j * 4 + 0]) - mean) * rstd * g.x + bb.x;
+            v[j * 4 + 1] = (__uint_as_float(r[j * 4 + 1]) - mean) * rstd * g.y + bb.y;
+            v[j * 4 + 2] = (__uint_as_float(r[j * 4 + 2]) - mean) * rstd * g.z + bb.z;
+            v[j * 4 + 3] = (__uint_as_float(r[j * 4 + 3]) - mean) * rstd * g.w + bb.w;
+          }
+        } else {
+          const float4* sb = reinterpret_cast<const float4*>(s_bias + n0 + c * 32);
+          const bool has_pe = p.pe != nullptr;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b4 = sb[j];
+            float x0 = __uint_as_float(r[j * 4 + 0]) + b4.x, x1 = __uint_as_float(r[j * 4 + 1]) + b4.y;
+            float x2 = __uint_as_float(r[j * 4 + 2]) + b4.z, x3 = __uint_as_float(r[j * 4 + 3]) + b4.w;
+            if (p.act == ACT_RELU) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); x2 = fmaxf(x2, 0.f); x3 = fmaxf(x3, 0.f); }
+            else if (p.act == ACT_TANH) { x0 = fast_tanh(x0); x1 = fast_tanh(x1); x2 = fast_tanh(x2); x3 = fast_tanh(x3); }
+            if (has_pe) { x0 += v[j * 4 + 0]; x1 += v[j * 4 + 1]; x2 += v[j * 4 + 2]; x3 += v[j * 4 + 3]; }
+            v[j * 4 + 0] = x0; v[j * 4 + 1] = x1; v[j * 4 + 2] = x2; v[j * 4 + 3] = x3;
+          }
+        }
+        uint8_t* ws = my_row + (c >> 1) * SLAB_BYTES;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 u;
+          u.x = pack_bf16(v[j * 8 + 0], v[j * 8 + 1]); u.y = pack_bf16(v[j * 8 + 2], v[j * 8 + 3]);
+          u.z = pack_bf16(v[j * 8 + 4], v[j * 8 + 5]); u.w = pack_bf16(v[j * 8 + 6], v[j * 8 + 7]);
+          *reinterpret_cast<uint4*>(ws + ((static_cast<uint32_t>((c & 1) * 4 + j) ^ sw) << 4)) = u;
+        }
+        if (c & 1) {                                // slab (c >> 1) complete: publish it with one TMA store
+          fence_proxy_async();
+          if (!LN && leader) bulk_wait_read<2>();   // slab ((c>>1)+1)%4 of the previous round has been read out
+          named_bar_sync(1, 128);
+          if (leader) {
+            tma_store_3d(&tmO, slabs + (c >> 1) * SLAB_BYTES, n0 + (c >> 1) * 64, t0, b);
+            bulk_commit();
+          }
+        }
+      }
+    }
+    if (leader) bulk_wait<0>();                     // all stores complete before the CTA retires its smem
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------ host side
+static int g_sm_count = 0;
+
+template <bool LN>
+static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
+                           const CUtensorMap& tmR, const Dev& p, cudaStream_t s) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    if (cudaFuncSetAttribute(gemm2_kernel<LN>, cudaFuncAttributeMaxDynamicSharedMemorySize, TOTAL) != cudaSuccess)
+      return "cudaFuncSetAttribute(gemm2) failed";
+    attr_done = true;
+  }
+  if (g_sm_count == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || g_sm_count <= 0)
+      return "gemm2: cannot query the SM count";
+  }
+  const int grid = p.total_tiles < g_sm_count ? p.total_tiles : g_sm_count;
+  gemm2_kernel<LN><<<grid, THREADS, TOTAL, s>>>(tmA, tmW, tmO, tmR, p);
+  note_launch();
+  return cudaGetLastError() == cudaSuccess ? nullptr : "gemm2 kernel launch failed";
+}
+
+bool gemm2_supports(const GemmArgs& a) {
+  const bool ln = a.ln_g != nullptr;
+  if (a.N % BN != 0 || a.N > MAX_N) return false;
+  if (a.out_bf16 == nullptr || a.out_f32 != nullptr || a.out_last != nullptr || a.residual_f32 != nullptr) return false;
+  if (a.ld_bf16 % 8 != 0 || (reinterpret_cast<uintptr_t>(a.out_bf16) & 15) != 0) return false;
+  if (ln != (a.residual != nullptr)) return false;            // residual only together with LayerNorm
+  if (ln && (a.N != BN || a.pe != nullptr || a.act != ACT_NONE)) return false;
+  if (ln && (a.ld_res % 8 != 0 || (reinterpret_cast<uintptr_t>(a.residual) & 15) != 0)) return false;
+  return true;
+}
+
+const char* gemm2_launch(const GemmArgs& a, cudaStream_t s) {
+  Dev p;
+  p.T = a.T; p.N = a.N;
+  p.tap_off = a.tap_off; p.kc_per_tap = a.kc_per_tap; p.num_kb = a.taps * a.kc_per_tap;
+  p.tiles_per_utt = (a.T + BM - 1) / BM;
+  p.n_tiles = a.N / BN;
+  p.total_tiles = a.B * p.tiles_per_utt * p.n_tiles;
+  p.bias = a.bias; p.act = a.act;
+  p.pe = a.pe; p.alpha = a.alpha; p.pe_period = a.pe != nullptr ? a.pe_period : 1;
+  p.ln_g = a.ln_g; p.ln_b = a.ln_b;
+  p.has_res = a.residual != nullptr;
+  const int ktot = p.num_kb * BK;
+  CUtensorMap tmA, tmW, tmO, tmR;
+  const char* e = make_tmap_3d(&tmA, a.A, (uint64_t)a.C, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.C * 2,
+                               (uint64_t)a.T * a.C * 2, BK, BM);
+  if (e) return e;
+  e = make_tmap_3d(&tmW, a.W, (uint64_t)ktot, (uint64_t)a.N, 1, (uint64_t)ktot * 2, (uint64_t)ktot * 2 * a.N, BK, BN);
+  if (e) return e;
+  e = make_tmap_3d(&tmO, a.out_bf16, (uint64_t)a.N, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_bf16 * 2,
+                   (uint64_t)a.T * a.ld_bf16 * 2, 64, BM);
+  if (e) return e;
+  if (a.residual != nullptr) {
+    e = make_tmap_3d(&tmR, a.residual, (uint64_t)a.N, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_res * 2,
+                     (uint64_t)a.T * a.ld_res * 2, 64, BM);
+    if (e) return e;
+    return launch2<true>(tmA, tmW, tmO, tmR, p, s);
+  }
+  return launch2<false>(tmA, tmW, tmO, tmO, p, s);
+}
+
+}  // namespace tts

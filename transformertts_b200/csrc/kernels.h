@@ -46,6 +46,8 @@ struct GemmArgs {
 };
 
 const char* gemm_launch(const GemmArgs& a, cudaStream_t s);   // returns nullptr or an error string
+bool gemm2_supports(const GemmArgs& a);                        // persistent bf16-out kernel (gemm2.cu)
+const char* gemm2_launch(const GemmArgs& a, cudaStream_t s);
 
 // Fused masked-softmax attention over packed projections.
 // Q rows: q[(b*Tq + i)*ldq + h*64 + d], K/V likewise with Tk, ldk/ldv.  Keys j >= klen[b] are masked
