@@ -9,6 +9,8 @@
 // Round-1 implementation: flash-style online softmax, 128 query rows per CTA (8 warps x 16 rows),
 // 64-key tiles double-buffered with cp.async, bf16 mma.sync m16n8k16 with fp32 accumulate.
 // (tcgen05/TMEM version of this kernel is the next step; see DESIGN.md.)
+#include <stdlib.h>
+
 #include "kernels.h"
 #include "ptx.cuh"
 
@@ -253,6 +255,10 @@ attn_kernel(const AttnArgs a) {
 const char* attn_launch(const AttnArgs& a, cudaStream_t s) {
   if (a.B <= 0 || a.Tq <= 0 || a.Tk <= 0) return "attention: empty problem";
   if ((a.ldq | a.ldk | a.ldv | a.ldo) % 8 != 0) return "attention: leading dimensions must be multiples of 8";
+  {
+    static const bool force_v1 = getenv("TTS_ATTN_V1") != nullptr;
+    if (!force_v1 && attn2_supports(a)) return attn2_launch(a, s);
+  }
   static bool attr_done = false;
   if (!attr_done) {
     if (cudaFuncSetAttribute(attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(AttnSmem)) !=

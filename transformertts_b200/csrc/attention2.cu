@@ -1,0 +1,322 @@
+// Fused masked-softmax attention on tcgen05 / TMEM / TMA (head dim 64, sm_100a).
+//
+// Replaces nn.MultiheadAttention's core as the reference calls it: scores = (q/8) k^T + (-inf masks),
+// softmax over keys, P v (torch/nn/functional.py:6620-6665), masks of TransformerTTS._get_mask
+// (model/model.py:229-257) derived from per-utterance lengths, and the per-head cross-attention
+// probabilities of TransformerDecoderLayer._mha_block (model/layers.py:54-74) stored fp32 [B,H,Tq,Tk]
+// only when asked for.
+//
+// One CTA = 128 queries of one (utterance, head); keys stream in 64-row tiles.
+//   warp 0      TMA producer : Q tile once, then K/V tiles into a 4-stage ring (SWIZZLE_128B)
+//   warp 1      MMA issuer   : S = Q K^T (128x64x64) into one of two TMEM buffers, O += P V (128x64x64,
+//                              V consumed MN-major straight from its [key][dim] tile), fp32 accumulators in TMEM
+//   warps 2..5  softmax      : thread == query row: tcgen05.ld S -> masks -> online max/sum (exp2) -> bf16 P into a
+//                              swizzled smem tile (the A operand of P V); O is rescaled in TMEM only when the
+//                              running max grew by more than 2^8 (lazy rescale), normalised once at the end
+// Two CTAs share an SM (256 TMEM columns, ~97 KB smem each) so one CTA's softmax overlaps the other's MMAs.
+// With probs != nullptr a second sweep recomputes S per tile and stores exp2(s - m) / l through a padded smem
+// transpose so every row leaves as 128-byte coalesced segments.
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace tts {
+
+namespace a2 {
+constexpr int BQ = 128, BKV = 64, ST = 4;
+constexpr int THREADS = 192;
+constexpr int Q_BYTES = BQ * 64 * 2;            // 16 KB
+constexpr int KV_TILE = BKV * 64 * 2;           // 8 KB  (K or V)
+constexpr int STAGE_BYTES = 2 * KV_TILE;        // 16 KB
+constexpr int Q_OFF = 0;
+constexpr int KV_OFF = Q_BYTES;
+constexpr int P_OFF = KV_OFF + ST * STAGE_BYTES;            // 80 KB
+constexpr int P_BYTES = 17 * 1024;                          // 16 KB P tile; 16.5 KB as fp32 [128][33] staging
+constexpr int BAR_OFF = P_OFF + P_BYTES;
+constexpr int TOTAL = BAR_OFF + 256 + 1024;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLazy = 8.f;                    // rescale O only when the max grows by more than 2^8
+
+struct Dev {
+  bf16* O; int ldo;
+  float* probs;
+  const int* klen;
+  int Tq, Tk, causal;
+};
+}  // namespace a2
+
+using namespace a2;
+
+__device__ __forceinline__ uint32_t idesc_s() { return umma_idesc_bf16(BQ, BKV); }
+__device__ __forceinline__ uint32_t idesc_pv() { return umma_idesc_bf16(BQ, 64) | (1u << 16); }   // B is MN-major
+
+__global__ void __launch_bounds__(THREADS, 2)
+attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+             const __grid_constant__ CUtensorMap tmV, const Dev p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* q_full = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
+  uint64_t* kv_full = q_full + 1;        // [ST]
+  uint64_t* kv_empty = kv_full + ST;     // [ST]
+  uint64_t* s_full = kv_empty + ST;      // [2]
+  uint64_t* p_full = s_full + 2;         // [2]  softmax is done with S buffer (and P / O are ready)
+  uint64_t* pv_done = p_full + 2;        // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qt = gridDim.x - 1 - blockIdx.x;            // heavy (late, causal) tiles first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int q0 = qt * BQ;
+  const int klen = p.klen != nullptr ? min(__ldg(p.klen + b), p.Tk) : p.Tk;
+  int kv_end = klen;
+  if (p.causal) kv_end = min(kv_end, q0 + BQ);
+  const int n1 = (kv_end + BKV - 1) / BKV;                          // sweep 1: S, softmax, P V
+  const int n2 = p.probs != nullptr ? (p.Tk + BKV - 1) / BKV : 0;   // sweep 2: S again, probabilities out
+  const int n_all = n1 + n2;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < ST; ++s) { mbar_init(kv_full + s, 1); mbar_init(kv_empty + s, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(s_full + i, 1); mbar_init(p_full + i, 4); }
+    mbar_init(pv_done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t t_s0 = tmem_base, t_o = tmem_base + 128;          // S buffers at +0 / +64, O at +128
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      mbar_expect_tx(q_full, Q_BYTES);
+      tma_load_3d(smem + Q_OFF, &tmQ, q_full, h * kDh, q0, b);
+      int s = 0; uint32_t ph = 0;
+      for (int j = 0; j < n_all; ++j) {
+        const bool sweep2 = j >= n1;
+        const int k0 = (sweep2 ? j - n1 : j) * BKV;
+        mbar_wait(kv_empty + s, ph ^ 1);
+        uint8_t* st = smem + KV_OFF + s * STAGE_BYTES;
+        mbar_expect_tx(kv_full + s, sweep2 ? KV_TILE : STAGE_BYTES);
+        tma_load_3d(st, &tmK, kv_full + s, h * kDh, k0, b);
+        if (!sweep2) tma_load_3d(st + KV_TILE, &tmV, kv_full + s, h * kDh, k0, b);
+        if (++s == ST) { s = 0; ph ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      const uint32_t q_addr = smem_u32(smem + Q_OFF), p_addr = smem_u32(smem + P_OFF);
+      const uint64_t dq = umma_desc_sw128(q_addr), dp = umma_desc_sw128(p_addr);
+      mbar_wait(q_full, 0);
+      auto issue_s = [&](int j) {                       // S_j = Q K_j^T into buffer j & 1
+        const int s = j % ST;
+        mbar_wait(kv_full + s, (j / ST) & 1);
+        tc_fence_after();
+        const uint64_t dk = umma_desc_sw128(smem_u32(smem + KV_OFF + s * STAGE_BYTES));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) tc_mma_bf16(t_s0 + (j & 1) * 64, dq + 2 * k, dk + 2 * k, idesc_s(), k > 0 ? 1u : 0u);
+        tc_commit(s_full + (j & 1));
+        if (j >= n1) tc_commit(kv_empty + s);           // sweep 2 holds no V: the stage is free once S is done
+      };
+      issue_s(0);
+      if (n_all > 1) issue_s(1);
+      for (int j = 0; j < n_all; ++j) {
+        mbar_wait(p_full + (j & 1), (j >> 1) & 1);       // softmax consumed S_j (and wrote P_j, rescaled O)
+        tc_fence_after();
+        if (j < n1) {
+          const int s = j % ST;
+          const uint64_t dv = umma_desc_sw128(smem_u32(smem + KV_OFF + s * STAGE_BYTES + KV_TILE));
+#pragma unroll
+          for (int k = 0; k < 4; ++k)                    // 16 keys per step: P advances 32 B, V advances 16 rows
+            tc_mma_bf16(t_o, dp + 2 * k, dv + 128 * k, idesc_pv(), (j > 0 || k > 0) ? 1u : 0u);
+          tc_commit(kv_empty + s);
+          tc_commit(pv_done);
+        }
+        if (j + 2 < n_all) issue_s(j + 2);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------ softmax: thread == query row
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int qi = q0 + row;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    const uint32_t sw = static_cast<uint32_t>(row & 7);
+    uint8_t* p_row = smem + P_OFF + row * 128;
+    float m_run = -INFINITY, m_used = -INFINITY, l = 0.f;
+    const int row_lim = p.causal ? min(klen, qi + 1) : klen;   // keys [0, row_lim) are visible to this row
+
+    for (int j = 0; j < n1; ++j) {
+      mbar_wait(s_full + (j & 1), (j >> 1) & 1);
+      tc_fence_after();
+      uint32_t r[64];
+      {
+        uint32_t (&r0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&r[0]);
+        uint32_t (&r1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&r[32]);
+        tmem_ld32(t_s0 + (j & 1) * 64 + lane_off, r0);
+        tmem_ld32(t_s0 + (j & 1) * 64 + 32 + lane_off, r1);
+        tmem_ld_wait();
+      }
+      const int k0 = j * BKV;
+      const int nvis = row_lim - k0;                            // visible keys of this tile: [0, nvis)
+      float tmax = -INFINITY;
+#pragma unroll
+      for (int e = 0; e < 64; ++e) {
+        const float t = e < nvis ? __uint_as_float(r[e]) * kLog2e : -INFINITY;
+        r[e] = __float_as_uint(t);
+        tmax = fmaxf(tmax, t);
+      }
+      m_run = fmaxf(m_run, tmax);
+      float scale = 1.f;
+      bool grew = false;
+      if (m_run > m_used + kLazy || (m_used == -INFINITY && m_run > -INFINITY)) {
+        scale = m_used == -INFINITY ? 0.f : fast_exp2(m_used - m_run);
+        m_used = m_run;
+        l *= scale;
+        grew = true;
+      }
+      const float mref = m_used == -INFINITY ? 0.f : m_used;
+      float sum = 0.f;
+      uint32_t pk[32];
+#pragma unroll
+      for (int e = 0; e < 32; ++e) {
+        const float p0 = fast_exp2(__uint_as_float(r[2 * e]) - mref), p1 = fast_exp2(__uint_as_float(r[2 * e + 1]) - mref);
+        sum += p0 + p1;
+        pk[e] = pack_bf16(p0, p1);
+      }
+      l += sum;
+      if (j > 0) {                                              // P V of tile j-1 must be done with P and O
+        mbar_wait(pv_done, (j - 1) & 1);
+        tc_fence_after();
+        if (__any_sync(0xffffffffu, grew)) {
+          uint32_t o[32];
+#pragma unroll
+          for (int hlf = 0; hlf < 2; ++hlf) {
+            tmem_ld32(t_o + hlf * 32 + lane_off, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 32; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * scale);
+            tmem_st32(t_o + hlf * 32 + lane_off, o);
+          }
+          tmem_st_wait();
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(p_row + ((static_cast<uint32_t>(c) ^ sw) << 4)) =
+            make_uint4(pk[c * 4 + 0], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
+      fence_proxy_async();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full + (j & 1));
+    }
+
+    // ---- O = O / l -> bf16 -> global (one 128-byte row segment per thread)
+    mbar_wait(pv_done, (n1 - 1) & 1);
+    tc_fence_after();
+    const float inv = l > 0.f ? 1.f / l : 0.f;
+    {
+      uint32_t o[32];
+      bf16* og = p.O + ((size_t)b * p.Tq + qi) * p.ldo + h * kDh;
+#pragma unroll
+      for (int hlf = 0; hlf < 2; ++hlf) {
+        tmem_ld32(t_o + hlf * 32 + lane_off, o);
+        tmem_ld_wait();
+        if (qi < p.Tq) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint4 u;
+            u.x = pack_bf16(__uint_as_float(o[c * 8 + 0]) * inv, __uint_as_float(o[c * 8 + 1]) * inv);
+            u.y = pack_bf16(__uint_as_float(o[c * 8 + 2]) * inv, __uint_as_float(o[c * 8 + 3]) * inv);
+            u.z = pack_bf16(__uint_as_float(o[c * 8 + 4]) * inv, __uint_as_float(o[c * 8 + 5]) * inv);
+            u.w = pack_bf16(__uint_as_float(o[c * 8 + 6]) * inv, __uint_as_float(o[c * 8 + 7]) * inv);
+            *reinterpret_cast<uint4*>(og + hlf * 32 + c * 8) = u;
+          }
+        }
+      }
+    }
+
+    // ---- sweep 2: normalised probabilities, fp32 [B][H][Tq][Tk]
+    if (n2 > 0) {
+      const float mref = m_used == -INFINITY ? 0.f : m_used;
+      float* stage = reinterpret_cast<float*>(smem + P_OFF) + q * 32 * 33;      // this warp: [32 rows][33]
+      float* pg = p.probs + ((size_t)(b * kH + h) * p.Tq + q0 + q * 32) * p.Tk;
+      const int rows_here = min(32, p.Tq - (q0 + q * 32));
+      for (int j = n1; j < n_all; ++j) {
+        mbar_wait(s_full + (j & 1), (j >> 1) & 1);
+        tc_fence_after();
+        const int k0 = (j - n1) * BKV;
+        const int nvis = row_lim - k0;
+#pragma unroll
+        for (int hlf = 0; hlf < 2; ++hlf) {
+          uint32_t r[32];
+          tmem_ld32(t_s0 + (j & 1) * 64 + hlf * 32 + lane_off, r);
+          tmem_ld_wait();
+          if (hlf == 1) {                                    // S buffer fully read: release it to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(p_full + (j & 1));
+          }
+#pragma unroll
+          for (int e = 0; e < 32; ++e)
+            stage[lane * 33 + e] = (hlf * 32 + e) < nvis ? fast_exp2(__uint_as_float(r[e]) * kLog2e - mref) * inv : 0.f;
+          __syncwarp();
+          const int kc = k0 + hlf * 32 + lane;
+          if (kc < p.Tk) {
+#pragma unroll 8
+            for (int rr = 0; rr < 32; ++rr)
+              if (rr < rows_here) pg[(size_t)rr * p.Tk + kc] = stage[rr * 33 + lane];
+          }
+          __syncwarp();
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
+// ------------------------------------------------------------------ host side
+bool attn2_supports(const AttnArgs& a) {
+  auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  return al(a.Q) && al(a.K) && al(a.V) && al(a.O) && a.ldq % 8 == 0 && a.ldk % 8 == 0 && a.ldv % 8 == 0 &&
+         a.ldo % 8 == 0;
+}
+
+const char* attn2_launch(const AttnArgs& a, cudaStream_t s) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    if (cudaFuncSetAttribute(attn2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TOTAL) != cudaSuccess)
+      return "cudaFuncSetAttribute(attention2) failed";
+    attr_done = true;
+  }
+  CUtensorMap tmQ, tmK, tmV;
+  // each map covers one head's 64 columns at a time: dims (row pitch in elements, rows, batch)
+  const char* e = make_tmap_3d(&tmQ, a.Q, (uint64_t)kD, (uint64_t)a.Tq, (uint64_t)a.B, (uint64_t)a.ldq * 2,
+                               (uint64_t)a.Tq * a.ldq * 2, 64, BQ);
+  if (e) return e;
+  e = make_tmap_3d(&tmK, a.K, (uint64_t)kD, (uint64_t)a.Tk, (uint64_t)a.B, (uint64_t)a.ldk * 2,
+                   (uint64_t)a.Tk * a.ldk * 2, 64, BKV);
+  if (e) return e;
+  e = make_tmap_3d(&tmV, a.V, (uint64_t)kD, (uint64_t)a.Tk, (uint64_t)a.B, (uint64_t)a.ldv * 2,
+                   (uint64_t)a.Tk * a.ldv * 2, 64, BKV);
+  if (e) return e;
+  Dev p;
+  p.O = a.O; p.ldo = a.ldo; p.probs = a.probs; p.klen = a.klen;
+  p.Tq = a.Tq; p.Tk = a.Tk; p.causal = a.causal;
+  dim3 grid((a.Tq + BQ - 1) / BQ, kH, a.B);
+  attn2_kernel<<<grid, THREADS, TOTAL, s>>>(tmQ, tmK, tmV, p);
+  note_launch();
+  return cudaGetLastError() == cudaSuccess ? nullptr : "attention2 kernel launch failed";
+}
+
+}  // namespace tts

@@ -64,6 +64,8 @@ struct AttnArgs {
   int B, Tq, Tk, causal;
 };
 const char* attn_launch(const AttnArgs& a, cudaStream_t s);
+bool attn2_supports(const AttnArgs& a);                        // tcgen05 kernel (attention2.cu)
+const char* attn2_launch(const AttnArgs& a, cudaStream_t s);
 
 // small elementwise kernels
 const char* embed_launch(const int64_t* phoneme, const bf16* table, bf16* out, int n_tok, int n_phon,

@@ -179,6 +179,12 @@ __device__ __forceinline__ float fast_tanh(float x) {
   return 1.f - __fdividef(2.f, t + 1.f);
 }
 
+__device__ __forceinline__ float fast_exp2(float x) {   // MUFU.EX2; exp2(-inf) = 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // UMMA shared-memory descriptor for a K-major tile whose rows are 128 B (64 bf16) wide, laid out by
 // TMA with CU_TENSOR_MAP_SWIZZLE_128B: 8-row groups are 1024 B apart (SBO), LBO is unused (=1),
 // descriptor version 1 (Blackwell), layout type 2 = SWIZZLE_128B.  The tile base must be 1024 B aligned;
