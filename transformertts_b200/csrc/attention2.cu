@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(THREADS, 2)
 attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
              const __grid_constant__ CUtensorMap tmV, const Dev p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   uint64_t* q_full = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
   uint64_t* kv_full = q_full + 1;        // [ST]
   uint64_t* kv_empty = kv_full + ST;     // [ST]

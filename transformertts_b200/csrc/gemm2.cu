@@ -14,56 +14,87 @@
 // Replaces: nn.Linear / LinearNorm (model/module.py:36-53), Conv1d+BatchNorm1d of ConvNormBN
 // (model/module.py:18-19,28-33, BN folded), MultiheadAttention in/out projections (torch/nn/functional.py:5798,6665),
 // FFN + residual + LayerNorm (torch/nn/modules/transformer.py:951-982), PositionalEncoding (model/model.py:95).
+#include <stdlib.h>
+
 #include "kernels.h"
 #include "ptx.cuh"
 
 namespace tts {
 
 namespace g2 {
-constexpr int BM = 128, BN = 256, BK = 64, ST = 3;
+constexpr int BM = 128, BN = 256, BK = 64;
 constexpr int THREADS = 192;
 constexpr int A_BYTES = BM * BK * 2;               // 16 KB
 constexpr int B_BYTES = BN * BK * 2;               // 32 KB
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;     // 48 KB
 constexpr int SLAB_BYTES = BM * 64 * 2;            // 128 rows x 64 bf16 columns = 16 KB
-constexpr int SLAB_OFF = ST * STAGE_BYTES;         // 144 KB
-constexpr int BAR_OFF = SLAB_OFF + 4 * SLAB_BYTES; // 208 KB
-constexpr int PAR_OFF = BAR_OFF + 256;
 constexpr int MAX_N = 1024;
-constexpr int TOTAL = PAR_OFF + (MAX_N + 2 * BN) * 4 + 1024;
+
+// Shared-memory plan.  WS ("W stationary", K <= 256, one tap): the CTA owns one 256-wide n-tile, keeps its whole
+// W slice (up to 4 k-blocks = 128 KB) resident and streams only A tiles, which cuts the L2 -> SM traffic per
+// output tile from 192 KB to 64 KB (the K = 256 GEMMs of this model are L2-bandwidth bound otherwise).
+template <bool LN, bool WS>
+struct Plan {
+  static constexpr int W_BYTES = WS ? 4 * B_BYTES : 0;
+  static constexpr int ST = WS ? (LN ? 3 : 4) : 3;
+  static constexpr int STAGE_BYTES = WS ? A_BYTES : A_BYTES + B_BYTES;
+  static constexpr int RING_OFF = W_BYTES;
+  static constexpr int NSLAB = WS ? 2 : 4;
+  static constexpr int SLAB_OFF = RING_OFF + ST * STAGE_BYTES;
+  static constexpr int BAR_OFF = SLAB_OFF + NSLAB * SLAB_BYTES;
+  static constexpr int PAR_OFF = BAR_OFF + 256;
+  static constexpr int NBIAS = WS ? BN : MAX_N;
+  static constexpr int TOTAL = PAR_OFF + (NBIAS + (LN ? 2 * BN : 0)) * 4 + 1024;
+  static_assert(TOTAL <= 232448, "shared memory plan exceeds 227 KB");
+};
 
 struct Dev {
   int T, N;
   int tap_off, kc_per_tap, num_kb;
-  int tiles_per_utt, n_tiles, total_tiles;
+  int tiles_per_utt, n_tiles, m_tiles, total_tiles;
   const float* bias;
   int act;
   const float* pe; float alpha; int pe_period;
   const float* ln_g; const float* ln_b;
-  int has_res;
 };
 }  // namespace g2
 
 using namespace g2;
 
-template <bool LN>
+template <bool LN, bool WS>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
              const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const Dev p) {
+  using P = Plan<LN, WS>;
+  constexpr int ST = P::ST;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
+  uint8_t* smem = align_smem_1024(smem_raw);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + P::BAR_OFF);
   uint64_t* empty = full + ST;
   uint64_t* acc_full = empty + ST;      // [2]
   uint64_t* acc_empty = acc_full + 2;   // [2]
   uint64_t* res_full = acc_empty + 2;   // [4]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 4);
-  float* s_bias = reinterpret_cast<float*>(smem + PAR_OFF);   // [MAX_N]
-  float* s_lng = s_bias + MAX_N;                              // [256]
-  float* s_lnb = s_lng + BN;                                  // [256]
+  uint64_t* w_full = res_full + 4;      // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 1);
+  float* s_bias = reinterpret_cast<float*>(smem + P::PAR_OFF);   // [NBIAS]
+  float* s_lng = s_bias + P::NBIAS;                              // [256]
+  float* s_lnb = s_lng + BN;                                     // [256]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+
+  // tile walk: WS -> fixed n-tile per CTA, m-tiles strided; otherwise flat (m, n) list strided by the grid
+  const int ws_n = WS ? (int)(blockIdx.x % p.n_tiles) : 0;
+  const int ws_m0 = WS ? (int)(blockIdx.x / p.n_tiles) : 0;
+  const int ws_step = WS ? (int)(gridDim.x / p.n_tiles) : 0;
+  auto tile_at = [&](int i, int& m_tile, int& n_tile) -> bool {
+    if (WS) {
+      m_tile = ws_m0 + i * ws_step; n_tile = ws_n;
+      return m_tile < p.m_tiles;
+    }
+    const int tile = blockIdx.x + i * gridDim.x;
+    n_tile = tile % p.n_tiles; m_tile = tile / p.n_tiles;
+    return tile < p.total_tiles;
+  };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -73,6 +104,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     for (int s = 0; s < ST; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, 4); }
     for (int i = 0; i < 4; ++i) mbar_init(res_full + i, 1);
+    mbar_init(w_full, 1);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -80,7 +112,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tmem_relinquish();
   }
   if (warp >= 2) {
-    for (int i = threadIdx.x - 64; i < p.N; i += 128) s_bias[i] = __ldg(p.bias + i);
+    const int nb0 = WS ? ws_n * BN : 0;
+    const int nb = WS ? BN : p.N;
+    for (int i = threadIdx.x - 64; i < nb; i += 128) s_bias[i] = __ldg(p.bias + nb0 + i);
     if (LN)
       for (int i = threadIdx.x - 64; i < BN; i += 128) { s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
   }
@@ -92,18 +126,22 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
+      if (WS) {
+        mbar_expect_tx(w_full, p.num_kb * B_BYTES);
+        for (int kb = 0; kb < p.num_kb; ++kb) tma_load_3d(smem + kb * B_BYTES, &tmW, w_full, kb * BK, ws_n * BN, 0);
+      }
       int s = 0; uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+      int m_tile, n_tile;
+      for (int i = 0; tile_at(i, m_tile, n_tile); ++i) {
         const int b = m_tile / p.tiles_per_utt, t0 = (m_tile % p.tiles_per_utt) * BM, n0 = n_tile * BN;
         for (int kb = 0; kb < p.num_kb; ++kb) {
           const int tap = kb / p.kc_per_tap;
           const int kc = kb - tap * p.kc_per_tap;
           mbar_wait(empty + s, ph ^ 1);
-          mbar_expect_tx(full + s, STAGE_BYTES);
-          uint8_t* sa = smem + s * STAGE_BYTES;
+          mbar_expect_tx(full + s, P::STAGE_BYTES);
+          uint8_t* sa = smem + P::RING_OFF + s * P::STAGE_BYTES;
           tma_load_3d(sa, &tmA, full + s, kc * BK, t0 + tap + p.tap_off, b);
-          tma_load_3d(sa + A_BYTES, &tmW, full + s, kb * BK, n0, 0);
+          if (!WS) tma_load_3d(sa + A_BYTES, &tmW, full + s, kb * BK, n0, 0);
           if (++s == ST) { s = 0; ph ^= 1; }
         }
       }
@@ -114,8 +152,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
       int s = 0; uint32_t ph = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      int m_tile, n_tile;
+      if (WS) { mbar_wait(w_full, 0); tc_fence_after(); }
+      for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
         const int buf = it & 1;
         const uint32_t use = static_cast<uint32_t>(it >> 1);
         mbar_wait(acc_empty + buf, (use & 1) ^ 1);           // epilogue has drained this TMEM buffer
@@ -124,9 +163,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(full + s, ph);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+          const uint32_t sa = smem_u32(smem + P::RING_OFF + s * P::STAGE_BYTES);
           const uint64_t da = umma_desc_sw128(sa);
-          const uint64_t db = umma_desc_sw128(sa + A_BYTES);
+          const uint64_t db = umma_desc_sw128(WS ? smem_u32(smem + kb * B_BYTES) : sa + A_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
             tc_mma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
@@ -142,22 +181,25 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const int q = warp & 3;                        // TMEM lane quadrant of this warp
     const int row = q * 32 + lane;
     const bool leader = threadIdx.x == 64;
-    uint8_t* slabs = smem + SLAB_OFF;
+    uint8_t* slabs = smem + P::SLAB_OFF;
     const uint32_t sw = static_cast<uint32_t>(row & 7);
-    uint8_t* my_row = slabs + row * 128;           // + slab * SLAB_BYTES + ((chunk16 ^ sw) << 4)
-    int it = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-      const int n_tile = tile % p.n_tiles, m_tile = tile / p.n_tiles;
+    uint8_t* my_row = slabs + row * 128;           // + buffer * SLAB_BYTES + ((chunk16 ^ sw) << 4)
+    auto sbuf = [](int slab) { return WS ? (slab & 1) : slab; };
+    int m_tile, n_tile;
+    for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
       const int b = m_tile / p.tiles_per_utt, t0 = (m_tile % p.tiles_per_utt) * BM, n0 = n_tile * BN;
       const int buf = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
       const uint32_t tacc = tmem_base + buf * BN + (static_cast<uint32_t>(q * 32) << 16);
+      const float* sbias_tile = s_bias + (WS ? 0 : n0);
+      auto load_res = [&](int slab) {              // residual slab -> its buffer (leader only)
+        const int sbi = sbuf(slab);
+        mbar_expect_tx(res_full + sbi, SLAB_BYTES);
+        tma_load_3d(slabs + sbi * SLAB_BYTES, &tmR, res_full + sbi, slab * 64, t0, b);
+      };
       if (LN && leader) {
         bulk_wait_read<0>();                       // the previous tile's stores have left the slabs
-        for (int s = 0; s < 4; ++s) {
-          mbar_expect_tx(res_full + s, SLAB_BYTES);
-          tma_load_3d(slabs + s * SLAB_BYTES, &tmR, res_full + s, s * 64, t0, b);
-        }
+        for (int s = 0; s < P::NSLAB; ++s) load_res(s);
       }
       mbar_wait(acc_full + buf, use & 1);
       tc_fence_after();
@@ -170,14 +212,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         for (int c = 0; c < 8; ++c) {
           uint32_t r[32];
           tmem_ld32(tacc + c * 32, r);
-          if ((c & 1) == 0) mbar_wait(res_full + (c >> 1), it & 1);
-          const uint8_t* rs = my_row + (c >> 1) * SLAB_BYTES;
+          if ((c & 1) == 0) mbar_wait(res_full + sbuf(c >> 1), WS ? ((2 * it + (c >> 2)) & 1) : (it & 1));
+          const uint8_t* rs = my_row + sbuf(c >> 1) * SLAB_BYTES;
           uint4 res[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j)
             res[j] = *reinterpret_cast<const uint4*>(rs + ((static_cast<uint32_t>((c & 1) * 4 + j) ^ sw) << 4));
           tmem_ld_wait();
-          const float4* sb = reinterpret_cast<const float4*>(s_bias + c * 32);
+          const float4* sb = reinterpret_cast<const float4*>(sbias_tile + c * 32);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float4 b0 = sb[2 * j], b1 = sb[2 * j + 1];
@@ -192,6 +234,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             for (int e = 0; e < 8; ++e) { sum += v[e]; sq += v[e] * v[e]; r[j * 8 + e] = __float_as_uint(v[e]); }
           }
           tmem_st32(tacc + c * 32, r);
+          if (WS && (c == 1 || c == 3)) {           // residual slab c>>1 consumed by everyone: refill its buffer
+            named_bar_sync(2, 128);
+            if (leader) load_res((c >> 1) + 2);
+          }
         }
         tmem_st_wait();
         mean = sum * (1.f / BN);
@@ -232,20 +278,29 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             v[j * 4 + 3] = (__uint_as_float(r[j * 4 + 3]) - mean) * rstd * g.w + bb.w;
           }
         } else {
-          const float4* sb = reinterpret_cast<const float4*>(s_bias + n0 + c * 32);
-          const bool has_pe = p.pe != nullptr;
+          const float4* sb = reinterpret_cast<const float4*>(sbias_tile + c * 32);
+          float x[32];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float4 b4 = sb[j];
-            float x0 = __uint_as_float(r[j * 4 + 0]) + b4.x, x1 = __uint_as_float(r[j * 4 + 1]) + b4.y;
-            float x2 = __uint_as_float(r[j * 4 + 2]) + b4.z, x3 = __uint_as_float(r[j * 4 + 3]) + b4.w;
-            if (p.act == ACT_RELU) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); x2 = fmaxf(x2, 0.f); x3 = fmaxf(x3, 0.f); }
-            else if (p.act == ACT_TANH) { x0 = fast_tanh(x0); x1 = fast_tanh(x1); x2 = fast_tanh(x2); x3 = fast_tanh(x3); }
-            if (has_pe) { x0 += v[j * 4 + 0]; x1 += v[j * 4 + 1]; x2 += v[j * 4 + 2]; x3 += v[j * 4 + 3]; }
-            v[j * 4 + 0] = x0; v[j * 4 + 1] = x1; v[j * 4 + 2] = x2; v[j * 4 + 3] = x3;
+            x[j * 4 + 0] = __uint_as_float(r[j * 4 + 0]) + b4.x; x[j * 4 + 1] = __uint_as_float(r[j * 4 + 1]) + b4.y;
+            x[j * 4 + 2] = __uint_as_float(r[j * 4 + 2]) + b4.z; x[j * 4 + 3] = __uint_as_float(r[j * 4 + 3]) + b4.w;
           }
+          if (p.act == ACT_RELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+          } else if (p.act == ACT_TANH) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] = fast_tanh(x[j]);
+          }
+          if (p.pe != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] += v[j];
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = x[j];
         }
-        uint8_t* ws = my_row + (c >> 1) * SLAB_BYTES;
+        uint8_t* ws = my_row + sbuf(c >> 1) * SLAB_BYTES;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           uint4 u;
@@ -255,10 +310,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         }
         if (c & 1) {                                // slab (c >> 1) complete: publish it with one TMA store
           fence_proxy_async();
-          if (!LN && leader) bulk_wait_read<2>();   // slab ((c>>1)+1)%4 of the previous round has been read out
+          // the buffer the next slab goes into must have been read out by its previous store
+          if (leader) { if (WS) bulk_wait_read<0>(); else if (!LN) bulk_wait_read<2>(); }
           named_bar_sync(1, 128);
           if (leader) {
-            tma_store_3d(&tmO, slabs + (c >> 1) * SLAB_BYTES, n0 + (c >> 1) * 64, t0, b);
+            tma_store_3d(&tmO, slabs + sbuf(c >> 1) * SLAB_BYTES, n0 + (c >> 1) * 64, t0, b);
             bulk_commit();
           }
         }
@@ -274,12 +330,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 // ------------------------------------------------------------------ host side
 static int g_sm_count = 0;
 
-template <bool LN>
+template <bool LN, bool WS>
 static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
                            const CUtensorMap& tmR, const Dev& p, cudaStream_t s) {
+  using P = Plan<LN, WS>;
   static bool attr_done = false;
   if (!attr_done) {
-    if (cudaFuncSetAttribute(gemm2_kernel<LN>, cudaFuncAttributeMaxDynamicSharedMemorySize, TOTAL) != cudaSuccess)
+    if (cudaFuncSetAttribute(gemm2_kernel<LN, WS>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::TOTAL) !=
+        cudaSuccess)
       return "cudaFuncSetAttribute(gemm2) failed";
     attr_done = true;
   }
@@ -289,8 +347,9 @@ static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const
         cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || g_sm_count <= 0)
       return "gemm2: cannot query the SM count";
   }
-  const int grid = p.total_tiles < g_sm_count ? p.total_tiles : g_sm_count;
-  gemm2_kernel<LN><<<grid, THREADS, TOTAL, s>>>(tmA, tmW, tmO, tmR, p);
+  int grid = p.total_tiles < g_sm_count ? p.total_tiles : g_sm_count;
+  if (WS) grid = (grid / p.n_tiles) * p.n_tiles;          // every CTA owns one n-tile
+  gemm2_kernel<LN, WS><<<grid, THREADS, P::TOTAL, s>>>(tmA, tmW, tmO, tmR, p);
   note_launch();
   return cudaGetLastError() == cudaSuccess ? nullptr : "gemm2 kernel launch failed";
 }
@@ -312,12 +371,14 @@ const char* gemm2_launch(const GemmArgs& a, cudaStream_t s) {
   p.tap_off = a.tap_off; p.kc_per_tap = a.kc_per_tap; p.num_kb = a.taps * a.kc_per_tap;
   p.tiles_per_utt = (a.T + BM - 1) / BM;
   p.n_tiles = a.N / BN;
-  p.total_tiles = a.B * p.tiles_per_utt * p.n_tiles;
+  p.m_tiles = a.B * p.tiles_per_utt;
+  p.total_tiles = p.m_tiles * p.n_tiles;
   p.bias = a.bias; p.act = a.act;
   p.pe = a.pe; p.alpha = a.alpha; p.pe_period = a.pe != nullptr ? a.pe_period : 1;
   p.ln_g = a.ln_g; p.ln_b = a.ln_b;
-  p.has_res = a.residual != nullptr;
   const int ktot = p.num_kb * BK;
+  static const bool no_ws = getenv("TTS_GEMM_NO_WS") != nullptr;
+  const bool ws = !no_ws && a.taps == 1 && p.num_kb <= 4;
   CUtensorMap tmA, tmW, tmO, tmR;
   const char* e = make_tmap_3d(&tmA, a.A, (uint64_t)a.C, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.C * 2,
                                (uint64_t)a.T * a.C * 2, BK, BM);
@@ -331,9 +392,9 @@ const char* gemm2_launch(const GemmArgs& a, cudaStream_t s) {
     e = make_tmap_3d(&tmR, a.residual, (uint64_t)a.N, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_res * 2,
                      (uint64_t)a.T * a.ld_res * 2, 64, BM);
     if (e) return e;
-    return launch2<true>(tmA, tmW, tmO, tmR, p, s);
+    return ws ? launch2<true, true>(tmA, tmW, tmO, tmR, p, s) : launch2<true, false>(tmA, tmW, tmO, tmR, p, s);
   }
-  return launch2<false>(tmA, tmW, tmO, tmO, p, s);
+  return ws ? launch2<false, true>(tmA, tmW, tmO, tmO, p, s) : launch2<false, false>(tmA, tmW, tmO, tmO, p, s);
 }
 
 }  // namespace tts

@@ -22,6 +22,12 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// 1024-byte aligned view of the dynamic shared memory that keeps the shared address space visible to the
+// compiler (so accesses become LDS/STS, not generic LD/ST)
+__device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* raw) {
+  return raw + ((1024u - (smem_u32(raw) & 1023u)) & 1023u);
+}
+
 // ---------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -53,6 +59,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // Bounded wait: a protocol bug must surface as a trapped kernel (an error the host reports),
 // never as a hung GPU box.  ~2^26 try_wait probes is seconds of wall time.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+#pragma unroll 1
   for (uint32_t i = 0; i < (1u << 26); ++i) {
     if (mbar_try_wait(bar, parity)) return;
   }
