@@ -31,6 +31,7 @@ extern "C" {
 
 /* flags */
 #define TTS_FLAG_WANT_ALIGN 1 /* tts_forward: store cross-attention probabilities into `align` */
+#define TTS_FLAG_SERIAL 4     /* tts_forward: run the encoder branch on the caller's stream instead of the side stream */
 #define TTS_FLAG_ENC_MASK 2   /* apply the phoneme key-padding mask in the encoder (forward: yes, inference: no) */
 
 /* activation codes for the operator-level entry points */

@@ -90,6 +90,23 @@ def test_forward_without_alignments_matches_with():
         assert torch.equal(a[k], b[k])        # same kernels, deterministic
 
 
+def test_forward_side_stream_matches_serial():
+    """The encoder branch runs on a side stream (fork/join events); results must equal the single-stream order
+    bit for bit, also when calls are issued back to back without a host sync."""
+    sd = O.make_state_dict(35)
+    ph, mel, pl, ml = O.make_inputs(5, 90, 300, seed=36)
+    m = _model(sd)
+    outs = [m(ph, mel, pl, ml) for _ in range(4)]
+    m.serial_encoder = True
+    ref = m(ph, mel, pl, ml)
+    torch.cuda.synchronize()
+    for o in outs:
+        for k in ("pred_melspec", "post_melspec", "pred_stop"):
+            assert torch.equal(o[k], ref[k]), k
+        for a, b in zip(o["alignments"], ref["alignments"]):
+            assert torch.equal(a, b)
+
+
 def test_forward_rejects_training_mode_and_bad_config():
     from transformertts_b200 import TransformerTTS
     sd = O.make_state_dict(33)

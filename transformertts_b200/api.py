@@ -18,7 +18,7 @@ import torch.nn as nn
 from . import _ext
 from .weights import D, FFN, KS, MAX_PE, N_MELS, PackedWeights
 
-FLAG_WANT_ALIGN, FLAG_ENC_MASK = 1, 2
+FLAG_WANT_ALIGN, FLAG_ENC_MASK, FLAG_SERIAL = 1, 2, 4
 
 
 class _Holder(nn.Module):
@@ -126,6 +126,7 @@ class TransformerTTS(nn.Module):
             raise ValueError(f"the sm_100a kernels are specialised to config.yaml:25-42; unsupported values: {bad}")
         self.device = torch.device(device)
         self.n_phon = n_phon
+        self.serial_encoder = False   # True: keep the encoder branch on the caller's stream (no side stream)
         self.strict_lens = False      # True: reproduce the reference's Tp == max(lens) assert (costs a host sync)
         for key, t in _reference_layout_init(n_phon).items():
             self._register(key, t.to(self.device))
@@ -200,7 +201,7 @@ class TransformerTTS(nn.Module):
             post = torch.empty_like(pred)
             stop = torch.empty(B, Tm, dtype=torch.float32, device=self.device)
             align = torch.empty(3, B, 4, Tm, Tp, dtype=torch.float32, device=self.device) if return_alignments else None
-            flags = FLAG_ENC_MASK | (FLAG_WANT_ALIGN if return_alignments else 0)
+            flags = FLAG_ENC_MASK | (FLAG_WANT_ALIGN if return_alignments else 0) | (FLAG_SERIAL if self.serial_encoder else 0)
             _ext.check(lib.tts_forward(C.byref(w.struct), _ext.ptr(phoneme), _ext.ptr(melspec), _ext.ptr(phoneme_lens),
                                        _ext.ptr(melspec_lens), B, Tp, Tm, flags, _ext.ptr(pred), _ext.ptr(post),
                                        _ext.ptr(stop), _ext.ptr(align), ws, ws_bytes, self._stream()), "tts_forward")

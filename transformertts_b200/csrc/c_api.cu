@@ -4,6 +4,7 @@
 #include "../../include/tts_b200.h"
 
 #include <math.h>
+#include <stdlib.h>
 #include <stdio.h>
 #include <string.h>
 
@@ -133,7 +134,7 @@ static Workspace carve(void* base, int B, int Tp, int Tm) {
   w.qkv_e = (bf16*)c.take(Np * 3 * kD * 2);
   w.att_e = (bf16*)c.take(Np * kD * 2);
   w.ffn_e = (bf16*)c.take(Np * kF * 2);
-  w.ckv = (bf16*)c.take(Np * 2 * kD * 2);
+  w.ckv = (bf16*)c.take(3 * Np * 2 * kD * 2);           // cross K/V of the memory, one [Np][512] block per decoder layer
   w.mel_in = (bf16*)c.take(Nm * kMel * 2);
   w.mel_pre16 = (bf16*)c.take(Nm * kMel * 2);
   w.d0 = (bf16*)c.take(Nm * kD * 2);
@@ -290,6 +291,29 @@ static int check_common(const TtsWeights* w, int B, int Tp, int Tm, const void* 
   return 0;
 }
 
+// ------------------------------------------------------------------ side stream for the encoder branch
+// The encoder (+ the per-layer cross K/V projections of its output) and the decoder front (prenet, layer-0
+// self-attention block) are independent until the first cross-attention; tts_forward runs the encoder branch on a
+// per-device side stream, forked from and joined back into the caller's stream with events, so its many small
+// launches fill the tails and launch gaps of the decoder kernels.
+#include <mutex>
+struct SideStream { cudaStream_t stream; cudaEvent_t fork, join; bool ok; };
+static SideStream* side_stream() {
+  static SideStream table[64] = {};
+  static std::mutex mu;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  SideStream& s = table[dev];
+  if (!s.ok) {
+    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    s.ok = true;
+  }
+  return &s;
+}
+
 // ------------------------------------------------------------------ TransformerTTS.forward
 extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const float* mel, const int64_t* ph_lens,
                            const int64_t* mel_lens, int B, int Tp, int Tm, int flags, float* mel_pre, float* mel_post,
@@ -301,8 +325,25 @@ extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const fl
   const int Np = B * Tp, Nm = B * Tm;
   TRY(lens_launch(ph_lens, ws.ph_len, B, 1, Tp, s));
   TRY(lens_launch(mel_lens, ws.mel_len, B, 1, Tm, s));
-  TRY(run_encoder(w, phoneme, B, Tp, (flags & TTS_FLAG_ENC_MASK) != 0, ws, s));
+  static const bool env_serial = getenv("TTS_SERIAL") != nullptr;
+  SideStream* side = (env_serial || (flags & TTS_FLAG_SERIAL)) ? nullptr : side_stream();
+  cudaStream_t se = s;                               // stream of the encoder branch
+  if (side != nullptr) {
+    if (cudaEventRecord(side->fork, s) != cudaSuccess || cudaStreamWaitEvent(side->stream, side->fork, 0) != cudaSuccess)
+      return fail("side stream fork failed");
+    se = side->stream;
+  }
+  const char* enc_err = run_encoder(w, phoneme, B, Tp, (flags & TTS_FLAG_ENC_MASK) != 0, ws, se);
   const bf16* memory = ws.e0;
+  for (int l = 0; l < 3 && enc_err == nullptr; ++l)
+    enc_err = run_cross_kv(w, l, memory, Np, ws.ckv + (size_t)l * Np * 2 * kD, se);
+  if (side != nullptr && cudaEventRecord(side->join, se) != cudaSuccess) return fail("side stream join failed");
+  struct JoinGuard {                                 // whatever path leaves this function, the caller's stream
+    SideStream* side; cudaStream_t s; bool joined;   // ends up ordered after the encoder branch
+    ~JoinGuard() { if (!joined) cudaStreamWaitEvent(s, side->join, 0); }
+  } guard{side, s, side == nullptr};
+  bool& joined = guard.joined;
+  if (enc_err != nullptr) return fail(enc_err);
 
   // decoder prenet on the go-frame-shifted target (model/model.py:278-279, 297): frame t reads mel[t-1]
   TRY(cast_mel_launch(mel, ws.mel_in, (size_t)Nm * kMel, s));
@@ -323,9 +364,13 @@ extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const fl
                       Tm, 1, s));
     TRY(proj_res_ln(ws.att_d, Nm, kD, L.sa.w_out, L.sa.b_out, x, L.ln1, y, s));            // y = LN1
     TRY(proj(y, Nm, kD, L.ca.w_in, L.ca.b_in, kD, ACT_NONE, ws.cq, s));
-    TRY(run_cross_kv(w, l, memory, Np, ws.ckv, s));
+    if (!joined) {                                   // first use of the encoder branch's results
+      if (cudaStreamWaitEvent(s, side->join, 0) != cudaSuccess) return fail("side stream join failed");
+      joined = true;
+    }
+    const bf16* ckv = ws.ckv + (size_t)l * Np * 2 * kD;
     float* probs = (flags & TTS_FLAG_WANT_ALIGN) ? align + (size_t)l * B * kH * Tm * Tp : nullptr;
-    TRY(run_attention(ws.cq, kD, ws.ckv, ws.ckv + kD, 2 * kD, ws.att_d, probs, ws.ph_len, B, Tm, Tp, 0, s));
+    TRY(run_attention(ws.cq, kD, ckv, ckv + kD, 2 * kD, ws.att_d, probs, ws.ph_len, B, Tm, Tp, 0, s));
     TRY(proj_res_ln(ws.att_d, Nm, kD, L.ca.w_out, L.ca.b_out, y, L.ln2, x, s));            // x = LN2
     TRY(proj(x, Nm, kD, L.ffn.w1, L.ffn.b1, kF, ACT_RELU, ws.ffn_d, s));
     TRY(proj_res_ln(ws.ffn_d, Nm, kF, L.ffn.w2, L.ffn.b2, x, L.ln3, y, s));                // y = LN3
