@@ -167,14 +167,21 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
       }
       const int k0 = j * BKV;
       const int nvis = row_lim - k0;                            // visible keys of this tile: [0, nvis)
-      float tmax = -INFINITY;
+      // raw scores stay in r[]; the exponent is one FFMA: exp2(s * log2e - m).  Only tiles that cross a mask
+      // boundary for some row of this warp pay for the per-element select.
+      if (!__all_sync(0xffffffffu, nvis >= BKV)) {
 #pragma unroll
-      for (int e = 0; e < 64; ++e) {
-        const float t = e < nvis ? __uint_as_float(r[e]) * kLog2e : -INFINITY;
-        r[e] = __float_as_uint(t);
-        tmax = fmaxf(tmax, t);
+        for (int e = 0; e < 64; ++e)
+          if (e >= nvis) r[e] = 0xff800000u;                    // -inf
       }
-      m_run = fmaxf(m_run, tmax);
+      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four chains: ILP, only 2 warps per scheduler
+#pragma unroll
+      for (int e = 0; e < 64; e += 4) {
+        mx[0] = fmaxf(mx[0], __uint_as_float(r[e])); mx[1] = fmaxf(mx[1], __uint_as_float(r[e + 1]));
+        mx[2] = fmaxf(mx[2], __uint_as_float(r[e + 2])); mx[3] = fmaxf(mx[3], __uint_as_float(r[e + 3]));
+      }
+      const float smax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      m_run = fmaxf(m_run, smax * kLog2e);
       float scale = 1.f;
       bool grew = false;
       if (m_run > m_used + kLazy || (m_used == -INFINITY && m_run > -INFINITY)) {
@@ -183,15 +190,17 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
         l *= scale;
         grew = true;
       }
-      const float mref = m_used == -INFINITY ? 0.f : m_used;
-      float sum = 0.f;
+      const float nmref = m_used == -INFINITY ? 0.f : -m_used;
+      float sm[4] = {0.f, 0.f, 0.f, 0.f};
       uint32_t pk[32];
 #pragma unroll
       for (int e = 0; e < 32; ++e) {
-        const float p0 = fast_exp2(__uint_as_float(r[2 * e]) - mref), p1 = fast_exp2(__uint_as_float(r[2 * e + 1]) - mref);
-        sum += p0 + p1;
+        const float p0 = fast_exp2(fmaf(__uint_as_float(r[2 * e]), kLog2e, nmref));
+        const float p1 = fast_exp2(fmaf(__uint_as_float(r[2 * e + 1]), kLog2e, nmref));
+        sm[e & 3] += p0 + p1;
         pk[e] = pack_bf16(p0, p1);
       }
+      const float sum = (sm[0] + sm[1]) + (sm[2] + sm[3]);
       l += sum;
       if (j > 0) {                                              // P V of tile j-1 must be done with P and O
         mbar_wait(pv_done, (j - 1) & 1);
@@ -246,7 +255,8 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
 
     // ---- sweep 2: normalised probabilities, fp32 [B][H][Tq][Tk]
     if (n2 > 0) {
-      const float mref = m_used == -INFINITY ? 0.f : m_used;
+      // exp2(s*log2e - m) / l == exp2(s*log2e - (m + log2 l))
+      const float nmref2 = (m_used == -INFINITY || !(l > 0.f)) ? -INFINITY : -(m_used + log2f(l));
       float* stage = reinterpret_cast<float*>(smem + P_OFF) + q * 32 * 33;      // this warp: [32 rows][33]
       float* pg = p.probs + ((size_t)(b * kH + h) * p.Tq + q0 + q * 32) * p.Tk;
       const int rows_here = min(32, p.Tq - (q0 + q * 32));
@@ -267,7 +277,7 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
           }
 #pragma unroll
           for (int e = 0; e < 32; ++e)
-            stage[lane * 33 + e] = (hlf * 32 + e) < nvis ? fast_exp2(__uint_as_float(r[e]) * kLog2e - mref) * inv : 0.f;
+            stage[lane * 33 + e] = (hlf * 32 + e) < nvis ? fast_exp2(fmaf(__uint_as_float(r[e]), kLog2e, nmref2)) : 0.f;
           __syncwarp();
           const int kc = k0 + hlf * 32 + lane;
           if (kc < p.Tk) {

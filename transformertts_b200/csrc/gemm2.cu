@@ -40,7 +40,8 @@ struct Plan {
   static constexpr int RING_OFF = W_BYTES;
   static constexpr int NSLAB = WS ? 2 : 4;
   static constexpr int SLAB_OFF = RING_OFF + ST * STAGE_BYTES;
-  static constexpr int BAR_OFF = SLAB_OFF + NSLAB * SLAB_BYTES;
+  static constexpr int ID_OFF = SLAB_OFF + NSLAB * SLAB_BYTES;       // 64x64 bf16 identity (residual via MMA)
+  static constexpr int BAR_OFF = ID_OFF + (LN ? 8192 : 0);
   static constexpr int PAR_OFF = BAR_OFF + 256;
   static constexpr int NBIAS = WS ? BN : MAX_N;
   static constexpr int TOTAL = PAR_OFF + (NBIAS + (LN ? 2 * BN : 0)) * 4 + 1024;
@@ -72,8 +73,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   uint64_t* empty = full + ST;
   uint64_t* acc_full = empty + ST;      // [2]
   uint64_t* acc_empty = acc_full + 2;   // [2]
-  uint64_t* res_full = acc_empty + 2;   // [4]
-  uint64_t* w_full = res_full + 4;      // [1]
+  uint64_t* w_full = acc_empty + 2;     // [1]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 1);
   float* s_bias = reinterpret_cast<float*>(smem + P::PAR_OFF);   // [NBIAS]
   float* s_lng = s_bias + P::NBIAS;                              // [256]
@@ -103,7 +103,6 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (LN) tma_prefetch_desc(&tmR);
     for (int s = 0; s < ST; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, 4); }
-    for (int i = 0; i < 4; ++i) mbar_init(res_full + i, 1);
     mbar_init(w_full, 1);
     fence_mbar_init();
   }
@@ -115,8 +114,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const int nb0 = WS ? ws_n * BN : 0;
     const int nb = WS ? BN : p.N;
     for (int i = threadIdx.x - 64; i < nb; i += 128) s_bias[i] = __ldg(p.bias + nb0 + i);
-    if (LN)
+    if (LN) {
       for (int i = threadIdx.x - 64; i < BN; i += 128) { s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
+      // 64x64 identity in the K-major SWIZZLE_128B operand layout: the residual tile is added to the accumulator
+      // by four extra N=64 MMAs (x * I, exact in fp32), so it rides the prefetched A pipeline instead of the epilogue
+      for (int ci = threadIdx.x - 64; ci < 512; ci += 128) {
+        const int n = ci >> 3, c16 = ci & 7;
+        const uint32_t one = (n >> 3) == c16 ? ((n & 1) ? 0x3F800000u : 0x00003F80u) : 0u;   // bf16 1.0 at k == n
+        const int wi = (n & 7) >> 1;
+        *reinterpret_cast<uint4*>(smem + P::ID_OFF + n * 128 + ((c16 ^ (n & 7)) << 4)) =
+            make_uint4(wi == 0 ? one : 0u, wi == 1 ? one : 0u, wi == 2 ? one : 0u, wi == 3 ? one : 0u);
+      }
+      fence_proxy_async();
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -134,14 +144,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       int m_tile, n_tile;
       for (int i = 0; tile_at(i, m_tile, n_tile); ++i) {
         const int b = m_tile / p.tiles_per_utt, t0 = (m_tile % p.tiles_per_utt) * BM, n0 = n_tile * BN;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
-          const int tap = kb / p.kc_per_tap;
-          const int kc = kb - tap * p.kc_per_tap;
+        for (int kb = 0; kb < p.num_kb + (LN ? 4 : 0); ++kb) {
           mbar_wait(empty + s, ph ^ 1);
-          mbar_expect_tx(full + s, P::STAGE_BYTES);
           uint8_t* sa = smem + P::RING_OFF + s * P::STAGE_BYTES;
-          tma_load_3d(sa, &tmA, full + s, kc * BK, t0 + tap + p.tap_off, b);
-          if (!WS) tma_load_3d(sa + A_BYTES, &tmW, full + s, kb * BK, n0, 0);
+          if (kb < p.num_kb) {
+            const int tap = kb / p.kc_per_tap;
+            const int kc = kb - tap * p.kc_per_tap;
+            mbar_expect_tx(full + s, P::STAGE_BYTES);
+            tma_load_3d(sa, &tmA, full + s, kc * BK, t0 + tap + p.tap_off, b);
+            if (!WS) tma_load_3d(sa + A_BYTES, &tmW, full + s, kb * BK, n0, 0);
+          } else {                                   // residual k-block: 64 columns of the residual tile
+            mbar_expect_tx(full + s, A_BYTES);
+            tma_load_3d(sa, &tmR, full + s, (kb - p.num_kb) * BK, t0, b);
+          }
           if (++s == ST) { s = 0; ph ^= 1; }
         }
       }
@@ -160,17 +175,26 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         mbar_wait(acc_empty + buf, (use & 1) ^ 1);           // epilogue has drained this TMEM buffer
         tc_fence_after();
         const uint32_t tacc = tmem_base + buf * BN;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        const int total_kb = p.num_kb + (LN ? 4 : 0);
+        for (int kb = 0; kb < total_kb; ++kb) {
           mbar_wait(full + s, ph);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + P::RING_OFF + s * P::STAGE_BYTES);
           const uint64_t da = umma_desc_sw128(sa);
-          const uint64_t db = umma_desc_sw128(WS ? smem_u32(smem + kb * B_BYTES) : sa + A_BYTES);
+          if (kb < p.num_kb) {
+            const uint64_t db = umma_desc_sw128(WS ? smem_u32(smem + kb * B_BYTES) : sa + A_BYTES);
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            tc_mma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k)
+              tc_mma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          } else {                                   // acc[:, 64r .. 64r+63] += residual k-block * I
+            constexpr uint32_t idesc64 = umma_idesc_bf16(BM, 64);
+            const uint64_t di = umma_desc_sw128(smem_u32(smem + P::ID_OFF));
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+              tc_mma_bf16(tacc + (kb - p.num_kb) * 64, da + 2 * k, di + 2 * k, idesc64, 1u);
+          }
           tc_commit(empty + s);
-          if (kb == p.num_kb - 1) tc_commit(acc_full + buf);
+          if (kb == total_kb - 1) tc_commit(acc_full + buf);
           if (++s == ST) { s = 0; ph ^= 1; }
         }
       }
@@ -192,54 +216,31 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       const uint32_t use = static_cast<uint32_t>(it >> 1);
       const uint32_t tacc = tmem_base + buf * BN + (static_cast<uint32_t>(q * 32) << 16);
       const float* sbias_tile = s_bias + (WS ? 0 : n0);
-      auto load_res = [&](int slab) {              // residual slab -> its buffer (leader only)
-        const int sbi = sbuf(slab);
-        mbar_expect_tx(res_full + sbi, SLAB_BYTES);
-        tma_load_3d(slabs + sbi * SLAB_BYTES, &tmR, res_full + sbi, slab * 64, t0, b);
-      };
-      if (LN && leader) {
-        bulk_wait_read<0>();                       // the previous tile's stores have left the slabs
-        for (int s = 0; s < P::NSLAB; ++s) load_res(s);
-      }
       mbar_wait(acc_full + buf, use & 1);
       tc_fence_after();
 
       float mean = 0.f, rstd = 1.f;
       if (LN) {
-        // pass 1: v = acc + bias + residual; row statistics; v parked back in TMEM
+        // pass 1: row statistics of v = acc + bias (the residual is already in the accumulator)
         float sum = 0.f, sq = 0.f;
 #pragma unroll 1
         for (int c = 0; c < 8; ++c) {
           uint32_t r[32];
           tmem_ld32(tacc + c * 32, r);
-          if ((c & 1) == 0) mbar_wait(res_full + sbuf(c >> 1), WS ? ((2 * it + (c >> 2)) & 1) : (it & 1));
-          const uint8_t* rs = my_row + sbuf(c >> 1) * SLAB_BYTES;
-          uint4 res[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            res[j] = *reinterpret_cast<const uint4*>(rs + ((static_cast<uint32_t>((c & 1) * 4 + j) ^ sw) << 4));
           tmem_ld_wait();
           const float4* sb = reinterpret_cast<const float4*>(sbias_tile + c * 32);
+          float s4[4] = {0.f, 0.f, 0.f, 0.f}, q4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float4 b0 = sb[2 * j], b1 = sb[2 * j + 1];
-            const float2 x0 = unpack_bf16(res[j].x), x1 = unpack_bf16(res[j].y), x2 = unpack_bf16(res[j].z),
-                         x3 = unpack_bf16(res[j].w);
-            float v[8];
-            v[0] = __uint_as_float(r[j * 8 + 0]) + b0.x + x0.x; v[1] = __uint_as_float(r[j * 8 + 1]) + b0.y + x0.y;
-            v[2] = __uint_as_float(r[j * 8 + 2]) + b0.z + x1.x; v[3] = __uint_as_float(r[j * 8 + 3]) + b0.w + x1.y;
-            v[4] = __uint_as_float(r[j * 8 + 4]) + b1.x + x2.x; v[5] = __uint_as_float(r[j * 8 + 5]) + b1.y + x2.y;
-            v[6] = __uint_as_float(r[j * 8 + 6]) + b1.z + x3.x; v[7] = __uint_as_float(r[j * 8 + 7]) + b1.w + x3.y;
-#pragma unroll
-            for (int e = 0; e < 8; ++e) { sum += v[e]; sq += v[e] * v[e]; r[j * 8 + e] = __float_as_uint(v[e]); }
+          for (int j = 0; j < 8; ++j) {
+            const float4 b4 = sb[j];
+            const float v0 = __uint_as_float(r[j * 4 + 0]) + b4.x, v1 = __uint_as_float(r[j * 4 + 1]) + b4.y;
+            const float v2 = __uint_as_float(r[j * 4 + 2]) + b4.z, v3 = __uint_as_float(r[j * 4 + 3]) + b4.w;
+            s4[0] += v0; s4[1] += v1; s4[2] += v2; s4[3] += v3;
+            q4[0] = fmaf(v0, v0, q4[0]); q4[1] = fmaf(v1, v1, q4[1]); q4[2] = fmaf(v2, v2, q4[2]); q4[3] = fmaf(v3, v3, q4[3]);
           }
-          tmem_st32(tacc + c * 32, r);
-          if (WS && (c == 1 || c == 3)) {           // residual slab c>>1 consumed by everyone: refill its buffer
-            named_bar_sync(2, 128);
-            if (leader) load_res((c >> 1) + 2);
-          }
+          sum += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+          sq += (q4[0] + q4[1]) + (q4[2] + q4[3]);
         }
-        tmem_st_wait();
         mean = sum * (1.f / BN);
         rstd = rsqrtf(fmaxf(sq * (1.f / BN) - mean * mean, 0.f) + 1e-5f);
       }
@@ -269,13 +270,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (LN) {
           const float4* g4 = reinterpret_cast<const float4*>(s_lng + c * 32);
           const float4* b4 = reinterpret_cast<const float4*>(s_lnb + c * 32);
+          const float4* sb4 = reinterpret_cast<const float4*>(sbias_tile + c * 32);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float4 g = g4[j], bb = b4[j];
-            v[j * 4 + 0] = (__uint_as_float(r[j * 4 + 0]) - mean) * rstd * g.x + bb.x;
-            v[j * 4 + 1] = (__uint_as_float(r[j * 4 + 1]) - mean) * rstd * g.y + bb.y;
-            v[j * 4 + 2] = (__uint_as_float(r[j * 4 + 2]) - mean) * rstd * g.z + bb.z;
-            v[j * 4 + 3] = (__uint_as_float(r[j * 4 + 3]) - mean) * rstd * g.w + bb.w;
+            const float4 g = g4[j], bb = b4[j], bi = sb4[j];
+            v[j * 4 + 0] = (__uint_as_float(r[j * 4 + 0]) + bi.x - mean) * (rstd * g.x) + bb.x;
+            v[j * 4 + 1] = (__uint_as_float(r[j * 4 + 1]) + bi.y - mean) * (rstd * g.y) + bb.y;
+            v[j * 4 + 2] = (__uint_as_float(r[j * 4 + 2]) + bi.z - mean) * (rstd * g.z) + bb.z;
+            v[j * 4 + 3] = (__uint_as_float(r[j * 4 + 3]) + bi.w - mean) * (rstd * g.w) + bb.w;
           }
         } else {
           const float4* sb = reinterpret_cast<const float4*>(sbias_tile + c * 32);
@@ -311,7 +313,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (c & 1) {                                // slab (c >> 1) complete: publish it with one TMA store
           fence_proxy_async();
           // the buffer the next slab goes into must have been read out by its previous store
-          if (leader) { if (WS) bulk_wait_read<0>(); else if (!LN) bulk_wait_read<2>(); }
+          if (leader) { if (WS) bulk_wait_read<0>(); else bulk_wait_read<2>(); }
           named_bar_sync(1, 128);
           if (leader) {
             tma_store_3d(&tmO, slabs + sbuf(c >> 1) * SLAB_BYTES, n0 + (c >> 1) * 64, t0, b);
