@@ -23,10 +23,10 @@ namespace tts {
 
 namespace g2 {
 constexpr int BM = 128, BN = 256, BK = 64;
-constexpr int THREADS = 192;
+constexpr int THREADS = 64 + 256;                  // producer warp, MMA warp, 8 epilogue warps
 constexpr int A_BYTES = BM * BK * 2;               // 16 KB
 constexpr int B_BYTES = BN * BK * 2;               // 32 KB
-constexpr int SLAB_BYTES = BM * 64 * 2;            // 128 rows x 64 bf16 columns = 16 KB
+constexpr int CHUNK_BYTES = BM * 32 * 2;           // 128 rows x 32 bf16 columns = 8 KB staging buffer
 constexpr int MAX_N = 1024;
 
 // Shared-memory plan.  WS ("W stationary", K <= 256, one tap): the CTA owns one 256-wide n-tile, keeps its whole
@@ -38,13 +38,13 @@ struct Plan {
   static constexpr int ST = WS ? (LN ? 3 : 4) : 3;
   static constexpr int STAGE_BYTES = WS ? A_BYTES : A_BYTES + B_BYTES;
   static constexpr int RING_OFF = W_BYTES;
-  static constexpr int NSLAB = WS ? 2 : 4;
+  static constexpr int NBUF_H = WS ? 2 : 3;                         // staging buffers per epilogue half
   static constexpr int SLAB_OFF = RING_OFF + ST * STAGE_BYTES;
-  static constexpr int ID_OFF = SLAB_OFF + NSLAB * SLAB_BYTES;       // 64x64 bf16 identity (residual via MMA)
+  static constexpr int ID_OFF = SLAB_OFF + 2 * NBUF_H * CHUNK_BYTES; // 64x64 bf16 identity (residual via MMA)
   static constexpr int BAR_OFF = ID_OFF + (LN ? 8192 : 0);
   static constexpr int PAR_OFF = BAR_OFF + 256;
   static constexpr int NBIAS = WS ? BN : MAX_N;
-  static constexpr int TOTAL = PAR_OFF + (NBIAS + (LN ? 2 * BN : 0)) * 4 + 1024;
+  static constexpr int TOTAL = PAR_OFF + (NBIAS + (LN ? 2 * BN : 0)) * 4 + (LN ? 4096 : 0) + 1024;  // + LN row partials
   static_assert(TOTAL <= 232448, "shared memory plan exceeds 227 KB");
 };
 
@@ -60,6 +60,18 @@ struct Dev {
 }  // namespace g2
 
 using namespace g2;
+
+// Four consecutive 32-column accumulator chunks of this thread's row, with the next tcgen05.ld in flight while
+// f(k, chunk) runs on the current one.
+template <class F>
+__device__ __forceinline__ void for_chunks4(uint32_t taddr, F&& f) {
+  uint32_t ra[32], rb[32];
+  tmem_ld32(taddr, ra);
+  tmem_ld_wait(); tmem_ld32(taddr + 32, rb); f(0, ra);
+  tmem_ld_wait(); tmem_ld32(taddr + 64, ra); f(1, rb);
+  tmem_ld_wait(); tmem_ld32(taddr + 96, rb); f(2, ra);
+  tmem_ld_wait(); f(3, rb);
+}
 
 template <bool LN, bool WS>
 __global__ void __launch_bounds__(THREADS, 1)
@@ -102,7 +114,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tma_prefetch_desc(&tmO);
     if (LN) tma_prefetch_desc(&tmR);
     for (int s = 0; s < ST; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, 8); }
     mbar_init(w_full, 1);
     fence_mbar_init();
   }
@@ -113,12 +125,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   if (warp >= 2) {
     const int nb0 = WS ? ws_n * BN : 0;
     const int nb = WS ? BN : p.N;
-    for (int i = threadIdx.x - 64; i < nb; i += 128) s_bias[i] = __ldg(p.bias + nb0 + i);
+    for (int i = threadIdx.x - 64; i < nb; i += 256) s_bias[i] = __ldg(p.bias + nb0 + i);
     if (LN) {
-      for (int i = threadIdx.x - 64; i < BN; i += 128) { s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
+      for (int i = threadIdx.x - 64; i < BN; i += 256) { s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
       // 64x64 identity in the K-major SWIZZLE_128B operand layout: the residual tile is added to the accumulator
       // by four extra N=64 MMAs (x * I, exact in fp32), so it rides the prefetched A pipeline instead of the epilogue
-      for (int ci = threadIdx.x - 64; ci < 512; ci += 128) {
+      for (int ci = threadIdx.x - 64; ci < 512; ci += 256) {
         const int n = ci >> 3, c16 = ci & 7;
         const uint32_t one = (n >> 3) == c16 ? ((n & 1) ? 0x3F800000u : 0x00003F80u) : 0u;   // bf16 1.0 at k == n
         const int wi = (n & 7) >> 1;
@@ -201,21 +213,29 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------ epilogue: thread == output row
+    // ------------------------------------------------------------ epilogue: 8 warps, thread == (output row, column half)
+    // Warps 2..5 own columns 0..127 of the tile, warps 6..9 columns 128..255 (two warps per TMEM lane quadrant, two
+    // per scheduler).  Each half walks its four 32-column chunks with the next tcgen05.ld in flight while the current
+    // chunk is processed, stages bf16 results in its own ring of 8 KB buffers (64-byte rows, SWIZZLE_64B) and
+    // publishes every chunk with one TMA store.
+    const int ew = warp - 2;
+    const int half = ew >> 2;
     const int q = warp & 3;                        // TMEM lane quadrant of this warp
     const int row = q * 32 + lane;
-    const bool leader = threadIdx.x == 64;
-    uint8_t* slabs = smem + P::SLAB_OFF;
-    const uint32_t sw = static_cast<uint32_t>(row & 7);
-    uint8_t* my_row = slabs + row * 128;           // + buffer * SLAB_BYTES + ((chunk16 ^ sw) << 4)
-    auto sbuf = [](int slab) { return WS ? (slab & 1) : slab; };
+    const bool leader = (ew & 3) == 0 && lane == 0;
+    constexpr int NB = P::NBUF_H;
+    uint8_t* bufs = smem + P::SLAB_OFF + half * (NB * CHUNK_BYTES);
+    const uint32_t sw = static_cast<uint32_t>((row >> 1) & 3);
+    uint8_t* my_row = bufs + row * 64;             // + buffer * CHUNK_BYTES + ((chunk16 ^ sw) << 4)
+    float2* s_stat = reinterpret_cast<float2*>(s_lnb + BN);     // [2 parities][2 halves][128 rows] (LN only)
+    int kc = 0;                                    // chunks this half has staged so far (selects the buffer)
     int m_tile, n_tile;
     for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
       const int b = m_tile / p.tiles_per_utt, t0 = (m_tile % p.tiles_per_utt) * BM, n0 = n_tile * BN;
       const int buf = it & 1;
       const uint32_t use = static_cast<uint32_t>(it >> 1);
-      const uint32_t tacc = tmem_base + buf * BN + (static_cast<uint32_t>(q * 32) << 16);
-      const float* sbias_tile = s_bias + (WS ? 0 : n0);
+      const uint32_t tacc = tmem_base + buf * BN + half * 128 + (static_cast<uint32_t>(q * 32) << 16);
+      const float* sbias_h = s_bias + (WS ? 0 : n0) + half * 128;
       mbar_wait(acc_full + buf, use & 1);
       tc_fence_after();
 
@@ -223,12 +243,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       if (LN) {
         // pass 1: row statistics of v = acc + bias (the residual is already in the accumulator)
         float sum = 0.f, sq = 0.f;
-#pragma unroll 1
-        for (int c = 0; c < 8; ++c) {
-          uint32_t r[32];
-          tmem_ld32(tacc + c * 32, r);
-          tmem_ld_wait();
-          const float4* sb = reinterpret_cast<const float4*>(sbias_tile + c * 32);
+        for_chunks4(tacc, [&](int k, const uint32_t (&r)[32]) {
+          const float4* sb = reinterpret_cast<const float4*>(sbias_h + k * 32);
           float s4[4] = {0.f, 0.f, 0.f, 0.f}, q4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -240,87 +256,81 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           }
           sum += (s4[0] + s4[1]) + (s4[2] + s4[3]);
           sq += (q4[0] + q4[1]) + (q4[2] + q4[3]);
-        }
+        });
+        float2* st = s_stat + (it & 1) * 256;
+        st[half * 128 + row] = make_float2(sum, sq);
+        named_bar_sync(3, 256);                      // both halves of every row have published their partial sums
+        const float2 o = st[(half ^ 1) * 128 + row];
+        sum += o.x; sq += o.y;
         mean = sum * (1.f / BN);
         rstd = rsqrtf(fmaxf(sq * (1.f / BN) - mean * mean, 0.f) + 1e-5f);
       }
 
       const int t_row = t0 + row;
       const int t_pe = p.pe != nullptr ? ((b * p.T + min(t_row, p.T - 1)) % p.pe_period) : 0;
-#pragma unroll 1
-      for (int c = 0; c < 8; ++c) {
-        uint32_t r[32];
-        tmem_ld32(tacc + c * 32, r);
-        float v[32];
-        if (!LN && p.pe != nullptr) {
-          const float4* pr = reinterpret_cast<const float4*>(p.pe + (size_t)t_pe * kD + n0 + c * 32);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 q4 = __ldg(pr + j);
-            v[j * 4 + 0] = p.alpha * q4.x; v[j * 4 + 1] = p.alpha * q4.y;
-            v[j * 4 + 2] = p.alpha * q4.z; v[j * 4 + 3] = p.alpha * q4.w;
-          }
-        }
-        tmem_ld_wait();
-        if (c == 7) {                               // last read of this TMEM buffer: hand it back to the MMA warp
+      for_chunks4(tacc, [&](int k, const uint32_t (&r)[32]) {
+        const int c = half * 4 + k;                  // chunk index within the 256-column tile
+        if (k == 3) {                                // last read of this TMEM buffer: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(acc_empty + buf);
         }
+        float v[32];
+        const float4* sb = reinterpret_cast<const float4*>(sbias_h + k * 32);
         if (LN) {
           const float4* g4 = reinterpret_cast<const float4*>(s_lng + c * 32);
           const float4* b4 = reinterpret_cast<const float4*>(s_lnb + c * 32);
-          const float4* sb4 = reinterpret_cast<const float4*>(sbias_tile + c * 32);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const float4 g = g4[j], bb = b4[j], bi = sb4[j];
+            const float4 g = g4[j], bb = b4[j], bi = sb[j];
             v[j * 4 + 0] = (__uint_as_float(r[j * 4 + 0]) + bi.x - mean) * (rstd * g.x) + bb.x;
             v[j * 4 + 1] = (__uint_as_float(r[j * 4 + 1]) + bi.y - mean) * (rstd * g.y) + bb.y;
             v[j * 4 + 2] = (__uint_as_float(r[j * 4 + 2]) + bi.z - mean) * (rstd * g.z) + bb.z;
             v[j * 4 + 3] = (__uint_as_float(r[j * 4 + 3]) + bi.w - mean) * (rstd * g.w) + bb.w;
           }
         } else {
-          const float4* sb = reinterpret_cast<const float4*>(sbias_tile + c * 32);
-          float x[32];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float4 b4 = sb[j];
-            x[j * 4 + 0] = __uint_as_float(r[j * 4 + 0]) + b4.x; x[j * 4 + 1] = __uint_as_float(r[j * 4 + 1]) + b4.y;
-            x[j * 4 + 2] = __uint_as_float(r[j * 4 + 2]) + b4.z; x[j * 4 + 3] = __uint_as_float(r[j * 4 + 3]) + b4.w;
+            v[j * 4 + 0] = __uint_as_float(r[j * 4 + 0]) + b4.x; v[j * 4 + 1] = __uint_as_float(r[j * 4 + 1]) + b4.y;
+            v[j * 4 + 2] = __uint_as_float(r[j * 4 + 2]) + b4.z; v[j * 4 + 3] = __uint_as_float(r[j * 4 + 3]) + b4.w;
           }
           if (p.act == ACT_RELU) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
           } else if (p.act == ACT_TANH) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) x[j] = fast_tanh(x[j]);
+            for (int j = 0; j < 32; ++j) v[j] = fast_tanh(v[j]);
           }
           if (p.pe != nullptr) {
+            const float4* pr = reinterpret_cast<const float4*>(p.pe + (size_t)t_pe * kD + n0 + c * 32);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) x[j] += v[j];
+            for (int j = 0; j < 8; ++j) {
+              const float4 q4 = __ldg(pr + j);
+              v[j * 4 + 0] = fmaf(p.alpha, q4.x, v[j * 4 + 0]); v[j * 4 + 1] = fmaf(p.alpha, q4.y, v[j * 4 + 1]);
+              v[j * 4 + 2] = fmaf(p.alpha, q4.z, v[j * 4 + 2]); v[j * 4 + 3] = fmaf(p.alpha, q4.w, v[j * 4 + 3]);
+            }
           }
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = x[j];
         }
-        uint8_t* ws = my_row + sbuf(c >> 1) * SLAB_BYTES;
+        const int bi = kc % NB;
+        uint8_t* ws = my_row + bi * CHUNK_BYTES;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           uint4 u;
           u.x = pack_bf16(v[j * 8 + 0], v[j * 8 + 1]); u.y = pack_bf16(v[j * 8 + 2], v[j * 8 + 3]);
           u.z = pack_bf16(v[j * 8 + 4], v[j * 8 + 5]); u.w = pack_bf16(v[j * 8 + 6], v[j * 8 + 7]);
-          *reinterpret_cast<uint4*>(ws + ((static_cast<uint32_t>((c & 1) * 4 + j) ^ sw) << 4)) = u;
+          *reinterpret_cast<uint4*>(ws + ((static_cast<uint32_t>(j) ^ sw) << 4)) = u;
         }
-        if (c & 1) {                                // slab (c >> 1) complete: publish it with one TMA store
-          fence_proxy_async();
-          // the buffer the next slab goes into must have been read out by its previous store
-          if (leader) { if (WS) bulk_wait_read<0>(); else bulk_wait_read<2>(); }
-          named_bar_sync(1, 128);
-          if (leader) {
-            tma_store_3d(&tmO, slabs + sbuf(c >> 1) * SLAB_BYTES, n0 + (c >> 1) * 64, t0, b);
-            bulk_commit();
-          }
+        fence_proxy_async();
+        // the buffer the next chunk goes into must have been read out by the store that last used it
+        if (leader) bulk_wait_read<NB - 2>();
+        named_bar_sync(1 + half, 128);
+        if (leader) {
+          tma_store_3d(&tmO, bufs + bi * CHUNK_BYTES, n0 + c * 32, t0, b);
+          bulk_commit();
         }
-      }
+        ++kc;
+      });
     }
     if (leader) bulk_wait<0>();                     // all stores complete before the CTA retires its smem
   }
@@ -388,7 +398,7 @@ const char* gemm2_launch(const GemmArgs& a, cudaStream_t s) {
   e = make_tmap_3d(&tmW, a.W, (uint64_t)ktot, (uint64_t)a.N, 1, (uint64_t)ktot * 2, (uint64_t)ktot * 2 * a.N, BK, BN);
   if (e) return e;
   e = make_tmap_3d(&tmO, a.out_bf16, (uint64_t)a.N, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_bf16 * 2,
-                   (uint64_t)a.T * a.ld_bf16 * 2, 64, BM);
+                   (uint64_t)a.T * a.ld_bf16 * 2, 32, BM, 64);
   if (e) return e;
   if (a.residual != nullptr) {
     e = make_tmap_3d(&tmR, a.residual, (uint64_t)a.N, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_res * 2,

@@ -75,6 +75,7 @@ const char* lens_launch(const int64_t* in, int* out, int n, int lo, int hi, cuda
 
 // tensor-map helper (driver entry point fetched through the runtime; no libcuda link dependency)
 const char* make_tmap_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
-                         uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1);
+                         uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1,
+                         int swizzle_bytes = 128);
 
 }  // namespace tts
