@@ -100,6 +100,10 @@ int tts_decode(const TtsWeights* w, const void* cross_kv, const int32_t* ph_len_
                int max_frames, float stop_threshold, void* self_kv, float* mel_out, float* stop_out,
                int32_t* stop_count, int32_t* n_frames, int rows_per_cluster, int cluster_size, void* stream);
 
+/* Number of thread-block clusters of the decode kernel the current device holds at once for a given plan
+ * (cudaOccupancyMaxActiveClusters); 0 if the plan cannot run. */
+int tts_decode_max_clusters(int rows_per_cluster, int cluster_size);
+
 /* PostNet with residual: mel_post = PostNet(mel_pre) + mel_pre, f32 [B][T][80] both. */
 int tts_postnet(const TtsWeights* w, const float* mel_pre, int B, int T, float* mel_post, void* workspace,
                 size_t ws_bytes, void* stream);

@@ -149,6 +149,9 @@ static Workspace carve(void* base, int B, int Tp, int Tm) {
 
 extern "C" int tts_abi_version(void) { return TTS_ABI_VERSION; }
 extern "C" const char* tts_last_error(void) { return g_err; }
+extern "C" int tts_decode_max_clusters(int rows_per_cluster, int cluster_size) {
+  return decode_max_clusters(rows_per_cluster, cluster_size);
+}
 extern "C" uint64_t tts_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 extern "C" size_t tts_workspace_bytes(int B, int Tp, int Tm) {
   if (B <= 0 || Tp <= 0 || Tm < 0) return 0;
@@ -440,12 +443,14 @@ extern "C" int tts_decode(const TtsWeights* w, const void* cross_kv, const int32
   a.mel_out = mel_out; a.stop_out = stop_out; a.stop_count = stop_count; a.n_frames = n_frames;
   if (cudaMemsetAsync(stop_count, 0, sizeof(int) * (size_t)max_frames, s) != cudaSuccess)
     return fail("cudaMemsetAsync(stop_count) failed");
-  int C = cluster_size > 0 ? cluster_size : 16;
-  int R = rows_per_cluster;
-  if (R <= 0) {                                      // fewest rows per cluster that still fits one wave
-    const int max_clusters = 148 / C;                // upper bound; GPC packing may allow fewer
+  int C = cluster_size, R = rows_per_cluster;
+  if (C <= 0 && R <= 0) {
+    decode_plan(B, &R, &C);
+  } else if (C <= 0) {
+    C = 16;
+  } else if (R <= 0) {                               // fewest rows per cluster that still fits one wave
     R = 1;
-    while (R < 8 && (B + R - 1) / R > (C == 16 ? 8 : max_clusters)) R *= 2;
+    while (R < 8 && (B + R - 1) / R > decode_max_clusters(R, C)) R *= 2;
   }
   TRY(decode_launch(a, R, C, s));
   return 0;

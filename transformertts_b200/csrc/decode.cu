@@ -430,6 +430,65 @@ static const char* launch_r(const DecodeArgs& a, int C, cudaStream_t s) {
   return cudaGetLastError() == cudaSuccess ? nullptr : "decode finalize launch failed";
 }
 
+// How many clusters of C CTAs of decode_kernel<R> the device can hold at once (0 on error).  A launch that needs
+// more than this runs in waves, i.e. the late clusters decode their utterances after the early ones finished.
+template <int R>
+static int max_clusters_r(int C) {
+  const size_t smem = sizeof(DecSmem<R>);
+  if (cudaFuncSetAttribute(decode_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
+  if (C > 8 && cudaFuncSetAttribute(decode_kernel<R>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
+    return 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(C * 64);
+  cfg.blockDim = dim3(DEC_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, decode_kernel<R>, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int decode_max_clusters(int R, int C) {
+  static int cache[9][17] = {};
+  if (R < 1 || R > 8 || C < 1 || C > 16) return 0;
+  if (cache[R][C] == 0) {
+    int n = 0;
+    switch (R) {
+      case 1: n = max_clusters_r<1>(C); break;
+      case 2: n = max_clusters_r<2>(C); break;
+      case 4: n = max_clusters_r<4>(C); break;
+      case 8: n = max_clusters_r<8>(C); break;
+      default: n = 0;
+    }
+    cache[R][C] = n > 0 ? n : -1;
+  }
+  return cache[R][C] > 0 ? cache[R][C] : 0;
+}
+
+// Rows per cluster / cluster size for a batch: everything must be co-resident (one wave); among the feasible plans
+// the cheapest by the measured per-step cost model  t(C, R) = base[C] + slope[C] * (R - 1)  wins
+// (B200: 16-CTA clusters have the lowest latency at one row, small clusters scale better with rows; profiles/).
+void decode_plan(int B, int* R_out, int* C_out) {
+  const int Cs[3] = {16, 8, 4};
+  const float base[3] = {58.f, 74.f, 100.f}, slope[3] = {58.f, 14.f, 24.f};
+  float best = 1e30f;
+  int bR = 8, bC = 4;
+  for (int ci = 0; ci < 3; ++ci) {
+    for (int R = 1; R <= 8; R *= 2) {
+      const int need = (B + R - 1) / R;
+      const int cap = decode_max_clusters(R, Cs[ci]);
+      if (cap <= 0 || need > cap) continue;
+      const float t = base[ci] + slope[ci] * (R - 1);
+      if (t < best) { best = t; bR = R; bC = Cs[ci]; }
+      break;                                           // larger R with the same C only costs more
+    }
+  }
+  *R_out = bR; *C_out = bC;
+}
+
 const char* decode_launch(const DecodeArgs& a, int R, int C, cudaStream_t s) {
   if (a.B <= 0 || a.Tmax <= 0 || a.Tp <= 0) return "decode: empty problem";
   if (a.B > 65535) return "decode: batch too large for the stop counter";

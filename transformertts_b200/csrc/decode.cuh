@@ -33,6 +33,8 @@ struct DecodeArgs {
   int* n_frames;                           // [1]
 };
 
+int decode_max_clusters(int rows_per_cluster, int cluster_size);   // co-resident clusters (occupancy query)
+void decode_plan(int B, int* rows_per_cluster, int* cluster_size);  // one-wave plan with the lowest modelled cost
 const char* decode_launch(const DecodeArgs& a, int rows_per_cluster, int cluster_size, cudaStream_t s);
 
 }  // namespace tts
