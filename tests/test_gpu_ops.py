@@ -122,7 +122,8 @@ def test_attention_causal_with_padding(B, T):
     _check("causal attention", o, ref, 8e-3, BF16_RTOL)
 
 
-@pytest.mark.parametrize("B,Tq,Tk", [(2, 200, 150), (1, 130, 37), (2, 64, 400), (1, 5, 3)])
+@pytest.mark.parametrize("B,Tq,Tk", [(2, 200, 150), (1, 130, 37), (2, 64, 400), (1, 5, 3), (2, 300, 256), (1, 128, 64),
+                                     (3, 100, 90), (2, 260, 33), (1, 4, 1)])
 def test_attention_cross_with_probabilities(B, Tq, Tk):
     g = torch.Generator().manual_seed(Tq * Tk)
     q, k, v = _qkv(B, Tq, Tk, g)

@@ -101,7 +101,7 @@ OPS = [
     ("dec cross-attn 800x150 +probs", lambda: attn(Tm, Tp, 0, True, False), 3),
     ("dec ffn1 51200x1024x256", lambda: linear(Nm, 1024, 256, act=1), 3),
     ("dec ffn2+LN 51200x256x1024", lambda: linear(Nm, 256, 1024, ln=True), 3),
-    ("heads 51200x81x256 f32", lambda: linear(Nm, 81, 256, f32=True), 1),
+    ("heads 51200x80x256 f32+bf16", lambda: linear(Nm, 80, 256, f32=True), 1),
     ("postnet conv 80->256 tanh", lambda: conv(B, Tm, 80, 256, act=2), 1),
     ("postnet conv 256->256 tanh", lambda: conv(B, Tm, 256, 256, act=2), 3),
     ("postnet conv 256->80 f32", lambda: conv(B, Tm, 256, 80, f32=True), 1),

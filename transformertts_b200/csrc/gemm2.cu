@@ -15,6 +15,7 @@
 // (model/module.py:18-19,28-33, BN folded), MultiheadAttention in/out projections (torch/nn/functional.py:5798,6665),
 // FFN + residual + LayerNorm (torch/nn/modules/transformer.py:951-982), PositionalEncoding (model/model.py:95).
 #include <stdlib.h>
+#include <string.h>
 
 #include "kernels.h"
 #include "ptx.cuh"
@@ -32,15 +33,20 @@ constexpr int MAX_N = 1024;
 // Shared-memory plan.  WS ("W stationary", K <= 256, one tap): the CTA owns one 256-wide n-tile, keeps its whole
 // W slice (up to 4 k-blocks = 128 KB) resident and streams only A tiles, which cuts the L2 -> SM traffic per
 // output tile from 192 KB to 64 KB (the K = 256 GEMMs of this model are L2-bandwidth bound otherwise).
-template <bool LN, bool WS>
+// F32 (fp32 heads / PostNet tail, N <= 128, never LN or WS): the first four epilogue warps stage 32-column fp32
+// chunks (128-byte rows, SWIZZLE_128B) plus an optional bf16 copy and publish both with TMA stores.
+constexpr int CHUNK32_BYTES = BM * 32 * 4;         // 16 KB
+template <bool LN, bool WS, bool F32 = false>
 struct Plan {
+  static_assert(!F32 || (!LN && !WS), "the fp32-output plan streams W and has no LayerNorm");
   static constexpr int W_BYTES = WS ? 4 * B_BYTES : 0;
   static constexpr int ST = WS ? (LN ? 3 : 4) : 3;
   static constexpr int STAGE_BYTES = WS ? A_BYTES : A_BYTES + B_BYTES;
   static constexpr int RING_OFF = W_BYTES;
   static constexpr int NBUF_H = WS ? 2 : 3;                         // staging buffers per epilogue half
   static constexpr int SLAB_OFF = RING_OFF + ST * STAGE_BYTES;
-  static constexpr int ID_OFF = SLAB_OFF + 2 * NBUF_H * CHUNK_BYTES; // 64x64 bf16 identity (residual via MMA)
+  static constexpr int SLAB_BYTES = F32 ? NBUF_H * (CHUNK32_BYTES + CHUNK_BYTES) : 2 * NBUF_H * CHUNK_BYTES;
+  static constexpr int ID_OFF = SLAB_OFF + SLAB_BYTES;               // 64x64 bf16 identity (residual via MMA)
   static constexpr int BAR_OFF = ID_OFF + (LN ? 8192 : 0);
   static constexpr int PAR_OFF = BAR_OFF + 256;
   static constexpr int NBIAS = WS ? BN : MAX_N;
@@ -56,6 +62,10 @@ struct Dev {
   int act;
   const float* pe; float alpha; int pe_period;
   const float* ln_g; const float* ln_b;
+  // fp32-output plan only
+  int n_mma, w_stage_bytes, n_main, has_bf16;      // MMA N (multiple of 16), bytes of one W k-block, columns stored
+  const float* res32; int ld_res32;                // fp32 residual [B*T][ld_res32] or null
+  float* out_last;                                 // column N-1 -> out_last[row] (stop head) or null
 };
 }  // namespace g2
 
@@ -73,11 +83,12 @@ __device__ __forceinline__ void for_chunks4(uint32_t taddr, F&& f) {
   tmem_ld_wait(); f(3, rb);
 }
 
-template <bool LN, bool WS>
+template <bool LN, bool WS, bool F32>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
              const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const Dev p) {
-  using P = Plan<LN, WS>;
+  // tmO: bf16 output (may be unused when F32 && !has_bf16); tmR: bf16 residual (LN) or the fp32 output (F32)
+  using P = Plan<LN, WS, F32>;
   constexpr int ST = P::ST;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
@@ -124,8 +135,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   }
   if (warp >= 2) {
     const int nb0 = WS ? ws_n * BN : 0;
-    const int nb = WS ? BN : p.N;
-    for (int i = threadIdx.x - 64; i < nb; i += 256) s_bias[i] = __ldg(p.bias + nb0 + i);
+    const int nb = WS ? BN : (F32 ? BN : p.N);
+    for (int i = threadIdx.x - 64; i < nb; i += 256) s_bias[i] = (!F32 || i < p.N) ? __ldg(p.bias + nb0 + i) : 0.f;
     if (LN) {
       for (int i = threadIdx.x - 64; i < BN; i += 256) { s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
       // 64x64 identity in the K-major SWIZZLE_128B operand layout: the residual tile is added to the accumulator
@@ -162,7 +173,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           if (kb < p.num_kb) {
             const int tap = kb / p.kc_per_tap;
             const int kc = kb - tap * p.kc_per_tap;
-            mbar_expect_tx(full + s, P::STAGE_BYTES);
+            mbar_expect_tx(full + s, F32 ? A_BYTES + p.w_stage_bytes : P::STAGE_BYTES);
             tma_load_3d(sa, &tmA, full + s, kc * BK, t0 + tap + p.tap_off, b);
             if (!WS) tma_load_3d(sa + A_BYTES, &tmW, full + s, kb * BK, n0, 0);
           } else {                                   // residual k-block: 64 columns of the residual tile
@@ -177,7 +188,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      const uint32_t idesc = F32 ? umma_idesc_bf16(BM, p.n_mma) : umma_idesc_bf16(BM, BN);
       int s = 0; uint32_t ph = 0;
       int m_tile, n_tile;
       if (WS) { mbar_wait(w_full, 0); tc_fence_after(); }
@@ -224,6 +235,104 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const int row = q * 32 + lane;
     const bool leader = (ew & 3) == 0 && lane == 0;
     constexpr int NB = P::NBUF_H;
+    if constexpr (F32) {
+      // ---- fp32-output plan: N <= 128, so only the first column half has work; the other four warps just hand
+      // the accumulator buffer back.  thread == output row; every 32-column chunk leaves as one fp32 TMA store
+      // (columns >= n_main and rows >= T are clipped by the tensor map) plus an optional bf16 copy.
+      uint8_t* fbufs = smem + P::SLAB_OFF;                         // NB x 16 KB, 128-byte rows, SWIZZLE_128B
+      uint8_t* hbufs = fbufs + NB * CHUNK32_BYTES;                 // NB x  8 KB,  64-byte rows, SWIZZLE_64B
+      const int n_chunks = (p.N + 31) >> 5;
+      const int last_chunk = (p.N - 1) >> 5, last_col = (p.N - 1) & 31;
+      const uint32_t sw8 = static_cast<uint32_t>(row & 7), sw4 = static_cast<uint32_t>((row >> 1) & 3);
+      int kc = 0;
+      int m_tile, n_tile;
+      for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
+        const int b = m_tile / p.tiles_per_utt, t0 = (m_tile % p.tiles_per_utt) * BM;
+        const int buf = it & 1;
+        const uint32_t use = static_cast<uint32_t>(it >> 1);
+        mbar_wait(acc_full + buf, use & 1);
+        tc_fence_after();
+        if (half == 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acc_empty + buf);
+          continue;
+        }
+        const uint32_t tacc = tmem_base + buf * BN + (static_cast<uint32_t>(q * 32) << 16);
+        const int t_row = t0 + row;
+        const bool valid = t_row < p.T;
+        const size_t grow = (size_t)b * p.T + (valid ? t_row : 0);
+        for (int k = 0; k < n_chunks; ++k) {
+          uint32_t r[32];
+          tmem_ld32(tacc + k * 32, r);
+          tmem_ld_wait();
+          if (k == n_chunks - 1) {                   // last read of this TMEM buffer
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty + buf);
+          }
+          float v[32];
+          const float4* sb = reinterpret_cast<const float4*>(s_bias + k * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b4 = sb[j];
+            v[j * 4 + 0] = __uint_as_float(r[j * 4 + 0]) + b4.x; v[j * 4 + 1] = __uint_as_float(r[j * 4 + 1]) + b4.y;
+            v[j * 4 + 2] = __uint_as_float(r[j * 4 + 2]) + b4.z; v[j * 4 + 3] = __uint_as_float(r[j * 4 + 3]) + b4.w;
+          }
+          if (p.act == ACT_RELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          } else if (p.act == ACT_TANH) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fast_tanh(v[j]);
+          }
+          if (p.res32 != nullptr && valid) {
+            const float4* rr = reinterpret_cast<const float4*>(p.res32 + grow * p.ld_res32 + k * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              if (k * 32 + j * 4 < p.n_main) {       // n_main % 4 == 0 when a residual is present
+                const float4 x = __ldg(rr + j);
+                v[j * 4 + 0] += x.x; v[j * 4 + 1] += x.y; v[j * 4 + 2] += x.z; v[j * 4 + 3] += x.w;
+              }
+            }
+          }
+          if (p.out_last != nullptr && k == last_chunk && valid) {
+            float z = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) z = j == last_col ? v[j] : z;
+            p.out_last[grow] = z;
+          }
+          const int bi = kc % NB;
+          uint8_t* wf = fbufs + bi * CHUNK32_BYTES + row * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(wf + ((static_cast<uint32_t>(j) ^ sw8) << 4)) =
+                make_float4(v[j * 4 + 0], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+          if (p.has_bf16) {
+            uint8_t* wh = hbufs + bi * CHUNK_BYTES + row * 64;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 u;
+              u.x = pack_bf16(v[j * 8 + 0], v[j * 8 + 1]); u.y = pack_bf16(v[j * 8 + 2], v[j * 8 + 3]);
+              u.z = pack_bf16(v[j * 8 + 4], v[j * 8 + 5]); u.w = pack_bf16(v[j * 8 + 6], v[j * 8 + 7]);
+              *reinterpret_cast<uint4*>(wh + ((static_cast<uint32_t>(j) ^ sw4) << 4)) = u;
+            }
+          }
+          fence_proxy_async();
+          if (leader) bulk_wait_read<NB - 2>();      // the buffer the next chunk goes into has been read out
+          named_bar_sync(1, 128);
+          if (leader) {
+            if (k * 32 < p.n_main) {
+              tma_store_3d(&tmR, fbufs + bi * CHUNK32_BYTES, k * 32, t0, b);
+              if (p.has_bf16) tma_store_3d(&tmO, hbufs + bi * CHUNK_BYTES, k * 32, t0, b);
+            }
+            bulk_commit();
+          }
+          ++kc;
+        }
+      }
+      if (leader) bulk_wait<0>();
+    } else {
     uint8_t* bufs = smem + P::SLAB_OFF + half * (NB * CHUNK_BYTES);
     const uint32_t sw = static_cast<uint32_t>((row >> 1) & 3);
     uint8_t* my_row = bufs + row * 64;             // + buffer * CHUNK_BYTES + ((chunk16 ^ sw) << 4)
@@ -333,6 +442,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       });
     }
     if (leader) bulk_wait<0>();                     // all stores complete before the CTA retires its smem
+    }  // !F32
   }
   tc_fence_before();
   __syncthreads();
@@ -342,13 +452,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 // ------------------------------------------------------------------ host side
 static int g_sm_count = 0;
 
-template <bool LN, bool WS>
+template <bool LN, bool WS, bool F32 = false>
 static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
                            const CUtensorMap& tmR, const Dev& p, cudaStream_t s) {
-  using P = Plan<LN, WS>;
+  using P = Plan<LN, WS, F32>;
   static bool attr_done = false;
   if (!attr_done) {
-    if (cudaFuncSetAttribute(gemm2_kernel<LN, WS>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::TOTAL) !=
+    if (cudaFuncSetAttribute(gemm2_kernel<LN, WS, F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::TOTAL) !=
         cudaSuccess)
       return "cudaFuncSetAttribute(gemm2) failed";
     attr_done = true;
@@ -361,40 +471,78 @@ static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const
   }
   int grid = p.total_tiles < g_sm_count ? p.total_tiles : g_sm_count;
   if (WS) grid = (grid / p.n_tiles) * p.n_tiles;          // every CTA owns one n-tile
-  gemm2_kernel<LN, WS><<<grid, THREADS, P::TOTAL, s>>>(tmA, tmW, tmO, tmR, p);
+  gemm2_kernel<LN, WS, F32><<<grid, THREADS, P::TOTAL, s>>>(tmA, tmW, tmO, tmR, p);
   note_launch();
   return cudaGetLastError() == cudaSuccess ? nullptr : "gemm2 kernel launch failed";
 }
 
+static bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
+
+// fp32-output plan: heads (N = 81: 80 mel columns + the stop logit) and the PostNet tail (N = 80, fp32 residual)
+static bool gemm2_supports_f32(const GemmArgs& a) {
+  if (a.out_f32 == nullptr || a.N > 128 || a.ln_g != nullptr || a.pe != nullptr || a.residual != nullptr) return false;
+  const int n_main = a.out_last != nullptr ? a.N - 1 : a.N;
+  if (n_main <= 0 || a.ld_f32 % 4 != 0 || !aligned16(a.out_f32)) return false;
+  if (a.out_bf16 != nullptr && (a.ld_bf16 % 8 != 0 || !aligned16(a.out_bf16))) return false;
+  if (a.residual_f32 != nullptr && (a.ld_res32 % 4 != 0 || n_main % 4 != 0 || !aligned16(a.residual_f32))) return false;
+  return true;
+}
+
 bool gemm2_supports(const GemmArgs& a) {
+  if (gemm2_supports_f32(a)) return true;
   const bool ln = a.ln_g != nullptr;
   if (a.N % BN != 0 || a.N > MAX_N) return false;
   if (a.out_bf16 == nullptr || a.out_f32 != nullptr || a.out_last != nullptr || a.residual_f32 != nullptr) return false;
-  if (a.ld_bf16 % 8 != 0 || (reinterpret_cast<uintptr_t>(a.out_bf16) & 15) != 0) return false;
+  if (a.ld_bf16 % 8 != 0 || !aligned16(a.out_bf16)) return false;
   if (ln != (a.residual != nullptr)) return false;            // residual only together with LayerNorm
   if (ln && (a.N != BN || a.pe != nullptr || a.act != ACT_NONE)) return false;
-  if (ln && (a.ld_res % 8 != 0 || (reinterpret_cast<uintptr_t>(a.residual) & 15) != 0)) return false;
+  if (ln && (a.ld_res % 8 != 0 || !aligned16(a.residual))) return false;
   return true;
 }
 
 const char* gemm2_launch(const GemmArgs& a, cudaStream_t s) {
   Dev p;
+  memset(&p, 0, sizeof(p));
   p.T = a.T; p.N = a.N;
   p.tap_off = a.tap_off; p.kc_per_tap = a.kc_per_tap; p.num_kb = a.taps * a.kc_per_tap;
   p.tiles_per_utt = (a.T + BM - 1) / BM;
-  p.n_tiles = a.N / BN;
   p.m_tiles = a.B * p.tiles_per_utt;
-  p.total_tiles = p.m_tiles * p.n_tiles;
   p.bias = a.bias; p.act = a.act;
   p.pe = a.pe; p.alpha = a.alpha; p.pe_period = a.pe != nullptr ? a.pe_period : 1;
   p.ln_g = a.ln_g; p.ln_b = a.ln_b;
   const int ktot = p.num_kb * BK;
-  static const bool no_ws = getenv("TTS_GEMM_NO_WS") != nullptr;
-  const bool ws = !no_ws && a.taps == 1 && p.num_kb <= 4;
   CUtensorMap tmA, tmW, tmO, tmR;
   const char* e = make_tmap_3d(&tmA, a.A, (uint64_t)a.C, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.C * 2,
                                (uint64_t)a.T * a.C * 2, BK, BM);
   if (e) return e;
+  if (gemm2_supports_f32(a)) {
+    p.n_tiles = 1; p.total_tiles = p.m_tiles;
+    p.n_mma = (a.N + 15) & ~15;
+    p.w_stage_bytes = p.n_mma * BK * 2;
+    p.n_main = a.out_last != nullptr ? a.N - 1 : a.N;
+    p.has_bf16 = a.out_bf16 != nullptr;
+    p.res32 = a.residual_f32; p.ld_res32 = a.ld_res32;
+    p.out_last = a.out_last;
+    // W rows [N, n_mma) are outside the tensor: TMA zero-fills them
+    e = make_tmap_3d(&tmW, a.W, (uint64_t)ktot, (uint64_t)a.N, 1, (uint64_t)ktot * 2, (uint64_t)ktot * 2 * a.N, BK,
+                     (uint32_t)p.n_mma);
+    if (e) return e;
+    e = make_tmap_3d(&tmR, a.out_f32, (uint64_t)p.n_main, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_f32 * 4,
+                     (uint64_t)a.T * a.ld_f32 * 4, 32, BM, 128, 4);
+    if (e) return e;
+    if (p.has_bf16) {
+      e = make_tmap_3d(&tmO, a.out_bf16, (uint64_t)p.n_main, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_bf16 * 2,
+                       (uint64_t)a.T * a.ld_bf16 * 2, 32, BM, 64);
+      if (e) return e;
+    } else {
+      tmO = tmR;
+    }
+    return launch2<false, false, true>(tmA, tmW, tmO, tmR, p, s);
+  }
+  p.n_tiles = a.N / BN;
+  p.total_tiles = p.m_tiles * p.n_tiles;
+  static const bool no_ws = getenv("TTS_GEMM_NO_WS") != nullptr;
+  const bool ws = !no_ws && a.taps == 1 && p.num_kb <= 4;
   e = make_tmap_3d(&tmW, a.W, (uint64_t)ktot, (uint64_t)a.N, 1, (uint64_t)ktot * 2, (uint64_t)ktot * 2 * a.N, BK, BN);
   if (e) return e;
   e = make_tmap_3d(&tmO, a.out_bf16, (uint64_t)a.N, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_bf16 * 2,

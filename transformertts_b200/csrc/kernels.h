@@ -66,6 +66,8 @@ struct AttnArgs {
 const char* attn_launch(const AttnArgs& a, cudaStream_t s);
 bool attn2_supports(const AttnArgs& a);                        // tcgen05 kernel (attention2.cu)
 const char* attn2_launch(const AttnArgs& a, cudaStream_t s);
+bool attn3_supports(const AttnArgs& a);                        // single-pass kernel, Tk <= 256 (attention3.cu)
+const char* attn3_launch(const AttnArgs& a, cudaStream_t s);
 
 // small elementwise kernels
 const char* embed_launch(const int64_t* phoneme, const bf16* table, bf16* out, int n_tok, int n_phon,
@@ -76,6 +78,6 @@ const char* lens_launch(const int64_t* in, int* out, int n, int lo, int hi, cuda
 // tensor-map helper (driver entry point fetched through the runtime; no libcuda link dependency)
 const char* make_tmap_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
                          uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1,
-                         int swizzle_bytes = 128);
+                         int swizzle_bytes = 128, int elem_bytes = 2);   // dims / boxes in elements of elem_bytes
 
 }  // namespace tts
