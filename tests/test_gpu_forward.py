@@ -86,8 +86,14 @@ def test_forward_without_alignments_matches_with():
     b = m(ph, mel, pl, ml, return_alignments=False)
     torch.cuda.synchronize()
     assert b["alignments"] == []
+    # storing the probabilities selects the single-pass cross-attention kernel, not storing them the streaming
+    # one: same math, different rounding points (bf16 P), so the outputs agree to bf16 noise, not bit for bit
     for k in ("pred_melspec", "post_melspec", "pred_stop"):
-        assert torch.equal(a[k], b[k])        # same kernels, deterministic
+        assert float((a[k] - b[k]).abs().max()) <= 0.15, k      # the stated forward tolerance
+    c = m(ph, mel, pl, ml, return_alignments=False)
+    torch.cuda.synchronize()
+    for k in ("pred_melspec", "post_melspec", "pred_stop"):
+        assert torch.equal(b[k], c[k])        # same kernels, deterministic
 
 
 def test_forward_side_stream_matches_serial():
