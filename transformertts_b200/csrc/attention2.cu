@@ -89,6 +89,8 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_launch();
+  griddep_wait();
   const uint32_t t_s0 = tmem_base, t_o = tmem_base + 128;          // S buffers at +0 / +64, O at +128
 
   if (warp == 0) {
@@ -324,9 +326,9 @@ const char* attn2_launch(const AttnArgs& a, cudaStream_t s) {
   p.O = a.O; p.ldo = a.ldo; p.probs = a.probs; p.klen = a.klen;
   p.Tq = a.Tq; p.Tk = a.Tk; p.causal = a.causal;
   dim3 grid((a.Tq + BQ - 1) / BQ, kH, a.B);
-  attn2_kernel<<<grid, THREADS, TOTAL, s>>>(tmQ, tmK, tmV, p);
+  const cudaError_t err = launch_pdl(attn2_kernel, grid, dim3(THREADS), TOTAL, s, tmQ, tmK, tmV, p);
   note_launch();
-  return cudaGetLastError() == cudaSuccess ? nullptr : "attention2 kernel launch failed";
+  return err == cudaSuccess ? nullptr : "attention2 kernel launch failed";
 }
 
 }  // namespace tts

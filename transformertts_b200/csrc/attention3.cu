@@ -87,6 +87,8 @@ attn3_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_launch();
+  griddep_wait();
   const uint32_t t_s = tmem_base + 64, t_o = tmem_base;  // O at columns 0..63, S at 64 .. 64 + 64 NT
 
   if (warp == 0) {
@@ -309,9 +311,9 @@ const char* attn3_launch(const AttnArgs& a, cudaStream_t s) {
   p.O = a.O; p.ldo = a.ldo; p.probs = a.probs; p.klen = a.klen;
   p.Tq = a.Tq; p.Tk = a.Tk; p.NT = NT;
   dim3 grid((a.Tq + BQ - 1) / BQ, kH, a.B);
-  attn3_kernel<<<grid, THREADS, bytes, s>>>(tmQ, tmK, tmV, p);
+  const cudaError_t err = launch_pdl(attn3_kernel, grid, dim3(THREADS), (size_t)bytes, s, tmQ, tmK, tmV, p);
   note_launch();
-  return cudaGetLastError() == cudaSuccess ? nullptr : "attention3 kernel launch failed";
+  return err == cudaSuccess ? nullptr : "attention3 kernel launch failed";
 }
 
 }  // namespace tts

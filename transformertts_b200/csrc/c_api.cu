@@ -30,6 +30,11 @@ static int fail(const char* msg) {
 static std::atomic<unsigned long long> g_launches{0};
 namespace tts {
 
+bool pdl_enabled() {
+  static const bool on = getenv("TTS_NO_PDL") == nullptr;
+  return on;
+}
+
 void note_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 __global__ void embed_kernel(const int64_t* __restrict__ ph, const uint4* __restrict__ table, uint4* __restrict__ out,

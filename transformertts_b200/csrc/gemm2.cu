@@ -155,6 +155,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_launch();
+  griddep_wait();                       // activations of the previous kernel are complete and visible from here on
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
@@ -471,9 +473,9 @@ static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const
   }
   int grid = p.total_tiles < g_sm_count ? p.total_tiles : g_sm_count;
   if (WS) grid = (grid / p.n_tiles) * p.n_tiles;          // every CTA owns one n-tile
-  gemm2_kernel<LN, WS, F32><<<grid, THREADS, P::TOTAL, s>>>(tmA, tmW, tmO, tmR, p);
+  const cudaError_t err = launch_pdl(gemm2_kernel<LN, WS, F32>, dim3(grid), dim3(THREADS), P::TOTAL, s, tmA, tmW, tmO, tmR, p);
   note_launch();
-  return cudaGetLastError() == cudaSuccess ? nullptr : "gemm2 kernel launch failed";
+  return err == cudaSuccess ? nullptr : "gemm2 kernel launch failed";
 }
 
 static bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }

@@ -75,6 +75,21 @@ const char* embed_launch(const int64_t* phoneme, const bf16* table, bf16* out, i
 const char* cast_mel_launch(const float* mel, bf16* out, size_t n, cudaStream_t s);
 const char* lens_launch(const int64_t* in, int* out, int n, int lo, int hi, cudaStream_t s);
 
+// Launch with programmatic stream serialization: the kernel's prologue (barrier init, TMEM allocation, tensor-map
+// prefetch) may overlap the tail of the previous kernel in the stream; the kernel itself calls griddepcontrol.wait
+// before it touches global memory.  TTS_NO_PDL=1 falls back to plain stream order.
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // tensor-map helper (driver entry point fetched through the runtime; no libcuda link dependency)
 const char* make_tmap_3d(CUtensorMap* m, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
                          uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1,
