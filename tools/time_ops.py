@@ -107,6 +107,11 @@ OPS = [
     ("postnet conv 256->80 f32", lambda: conv(B, Tm, 256, 80, f32=True), 1),
 ]
 
+if os.environ.get("TTS_TIME_OPS_EXTRA"):      # per-tile cost of the streaming attention kernel: time vs. key tiles per item
+    OPS += [("x self-attn dense 800x800", lambda: attn(Tm, Tm, 0, False, True), 0),
+            ("x self-attn dense 800x1600", lambda: attn(Tm, 1600, 0, False, False), 0),
+            ("x self-attn dense 800x3200", lambda: attn(Tm, 3200, 0, False, False), 0)]
+
 flt = sys.argv[1] if len(sys.argv) > 1 else ""
 total = 0.0
 for name, mk, count in OPS:
