@@ -13,7 +13,7 @@
  *   tts_encode           encoder half of TransformerTTS.inference   model/model.py:342-348
  *   tts_decode           AR loop of TransformerTTS.inference    model/model.py:351-384
  *   tts_postnet          PostNet + residual                     model/model.py:129-135, 310, 388
- *   tts_op_linear / tts_op_conv1d / tts_op_attention
+ *   tts_op_linear / tts_op_conv1d / tts_op_attention / tts_op_ffn
  *                        the torch.nn operators underneath (model/module.py:4-53,
  *                        torch/nn/functional.py:5798,6620-6665), exported for per-operator parity tests
  */
@@ -121,6 +121,12 @@ int tts_op_linear(const void* A, const void* W, const float* bias, int M, int N,
  * (Cpad = C rounded up to 64), + bias, act; optional f32 residual [B][T][N]. */
 int tts_op_conv1d(const void* x, const void* W, const float* bias, int B, int T, int C, int N, int taps,
                   int act, const float* residual_f32, void* out_bf16, float* out_f32, void* stream);
+
+/* Fused FFN block of a post-norm layer (torch/nn/modules/transformer.py:951-957, 980-982):
+ * out = LayerNorm(x + W2 relu(W1 x + b1) + b2); x, out bf16 [M][256] (distinct), w1 bf16 [1024][256],
+ * w2 bf16 [256][1024], b1 f32 [1024], b2 / ln_g / ln_b f32 [256].  The hidden activation stays on the SM. */
+int tts_op_ffn(const void* x, const void* w1, const float* b1, const void* w2, const float* b2, const float* ln_g,
+               const float* ln_b, int M, void* out, void* stream);
 
 /* Multi-head attention core, 4 heads x 64: q [B][Tq][ldq], k/v [B][Tk][ld] bf16 (q pre-scaled),
  * klen int32 [B] or NULL, causal 0/1, out bf16 [B][Tq][256], probs f32 [B][4][Tq][Tk] or NULL. */

@@ -153,3 +153,25 @@ def ref_attention(q, k, v, klen=None, causal=False):
     p = torch.softmax(s, dim=-1)
     o = (p @ vh).transpose(1, 2).reshape(B, Tq, 256)
     return o.float(), p.float()
+
+
+def op_ffn(x, w1, b1, w2, b2, ln):
+    """Fused FFN block through tts_op_ffn: LayerNorm(x + W2 relu(W1 x + b1) + b2), bf16 out."""
+    lib = _ext.load()
+    M = x.shape[0]
+    xd, w1d, w2d = dev_bf16(x), dev_bf16(w1), dev_bf16(w2)
+    b1d, b2d, g, b = dev_f32(b1), dev_f32(b2), dev_f32(ln[0]), dev_f32(ln[1])
+    out = torch.full((M, 256), float("nan"), dtype=torch.bfloat16, device=DEV)
+    _ext.check(lib.tts_op_ffn(_ext.ptr(xd), _ext.ptr(w1d), _ext.ptr(b1d), _ext.ptr(w2d), _ext.ptr(b2d), _ext.ptr(g),
+                              _ext.ptr(b), M, _ext.ptr(out), stream()), "tts_op_ffn")
+    torch.cuda.synchronize()
+    return out.float().cpu()
+
+
+def ref_ffn(x, w1, b1, w2, b2, ln, round_hidden=True):
+    h = torch.relu(x.double() @ w1.double().t() + b1.double())
+    if round_hidden:                      # the kernel keeps the hidden activation in bf16 (A operand of the 2nd GEMM)
+        h = h.float().to(torch.bfloat16).double()
+    y = x.double() + h @ w2.double().t() + b2.double()
+    y = torch.nn.functional.layer_norm(y, (256,), ln[0].double(), ln[1].double(), 1e-5)
+    return y.float()

@@ -4,7 +4,8 @@ accumulation-order noise; fp32 outputs only the latter."""
 import pytest
 import torch
 
-from parity_common import (bf16r, op_attention, op_conv1d, op_linear, ref_attention, ref_conv1d, ref_linear, report)
+from parity_common import (bf16r, op_attention, op_conv1d, op_ffn, op_linear, ref_attention, ref_conv1d, ref_ffn,
+                           ref_linear, report)
 
 pytestmark = pytest.mark.gpu
 
@@ -68,6 +69,18 @@ def test_linear_relu_positional_encoding():
     ref = ref_linear(A, W, b, act=1, pe=pe, alpha=0.7, pe_period=T)
     _check("linear+relu+PE f32", o32, ref, F32_ATOL, 1e-5)
     _check("linear+relu+PE bf16", o16, ref, BF16_ATOL, BF16_RTOL)
+
+
+# ------------------------------------------------------------------ fused FFN block (two GEMMs + residual + LayerNorm)
+@pytest.mark.parametrize("M", [128, 333, 1, 2048, 20000])
+def test_ffn_block(M):
+    g = torch.Generator().manual_seed(M)
+    x = _rand((M, 256), g)
+    w1, b1 = _rand((1024, 256), g, 1 / 16), torch.randn(1024, generator=g) * 0.1
+    w2, b2 = _rand((256, 1024), g, 1 / 32), torch.randn(256, generator=g) * 0.1
+    ln = (1 + 0.1 * torch.randn(256, generator=g), 0.05 * torch.randn(256, generator=g))
+    out = op_ffn(x, w1, b1, w2, b2, ln)
+    _check("ffn block bf16", out, ref_ffn(x, w1, b1, w2, b2, ln), 4e-3, BF16_RTOL)
 
 
 # ------------------------------------------------------------------ conv1d (implicit GEMM over taps)

@@ -50,6 +50,18 @@ def linear(M, N, K, act=0, ln=False, pe=False, f32=False):
     return fn, 2.0 * M * N * K
 
 
+def ffn(M):
+    x, w1, w2 = bf(M, 256), bf(1024, 256, scale=1 / 16), bf(256, 1024, scale=1 / 32)
+    b1, b2, g, b = (torch.zeros(1024, device=dev), torch.zeros(256, device=dev), torch.ones(256, device=dev),
+                    torch.zeros(256, device=dev))
+    out = torch.empty(M, 256, dtype=torch.bfloat16, device=dev)
+
+    def fn():
+        _ext.check(lib.tts_op_ffn(P(x), P(w1), P(b1), P(w2), P(b2), P(g), P(b), M, P(out), st()), "ffn")
+    fn.keep = (x, w1, w2, b1, b2, g, b, out)
+    return fn, 2.0 * M * 2 * 256 * 1024
+
+
 def conv(Bc, T, Cc, N, act=0, f32=False):
     Cp = (Cc + 63) // 64 * 64
     x, W, bias = bf(Bc, T, Cc), bf(N, 5 * Cp, scale=(5 * Cc) ** -0.5), torch.zeros(N, device=dev)
@@ -89,8 +101,9 @@ OPS = [
     ("enc qkv 9600x768x256", lambda: linear(Np, 768, 256), 3),
     ("enc attn 150x150", lambda: attn(Tp, Tp, 0, False, True), 3),
     ("enc out+LN 9600x256x256", lambda: linear(Np, 256, 256, ln=True), 3),
-    ("enc ffn1 9600x1024x256", lambda: linear(Np, 1024, 256, act=1), 3),
-    ("enc ffn2+LN 9600x256x1024", lambda: linear(Np, 256, 1024, ln=True), 3),
+    ("enc ffn fused 9600x256->1024->256 +LN", lambda: ffn(Np), 3),
+    ("enc ffn1 9600x1024x256 (unfused, not in the forward)", lambda: linear(Np, 1024, 256, act=1), 0),
+    ("enc ffn2+LN 9600x256x1024 (unfused)", lambda: linear(Np, 256, 1024, ln=True), 0),
     ("dec prenet1 51200x256x128", lambda: linear(Nm, 256, 128, act=1), 1),
     ("dec prenet2+PE 51200x256x256", lambda: linear(Nm, 256, 256, act=1, pe=True), 1),
     ("dec qkv 51200x768x256", lambda: linear(Nm, 768, 256), 3),
@@ -99,8 +112,9 @@ OPS = [
     ("dec cq 51200x256x256", lambda: linear(Nm, 256, 256), 3),
     ("dec ckv 9600x512x256", lambda: linear(Np, 512, 256), 3),
     ("dec cross-attn 800x150 +probs", lambda: attn(Tm, Tp, 0, True, False), 3),
-    ("dec ffn1 51200x1024x256", lambda: linear(Nm, 1024, 256, act=1), 3),
-    ("dec ffn2+LN 51200x256x1024", lambda: linear(Nm, 256, 1024, ln=True), 3),
+    ("dec ffn fused 51200x256->1024->256 +LN", lambda: ffn(Nm), 3),
+    ("dec ffn1 51200x1024x256 (unfused, not in the forward)", lambda: linear(Nm, 1024, 256, act=1), 0),
+    ("dec ffn2+LN 51200x256x1024 (unfused)", lambda: linear(Nm, 256, 1024, ln=True), 0),
     ("heads 51200x80x256 f32+bf16", lambda: linear(Nm, 80, 256, f32=True), 1),
     ("postnet conv 80->256 tanh", lambda: conv(B, Tm, 80, 256, act=2), 1),
     ("postnet conv 256->256 tanh", lambda: conv(B, Tm, 256, 256, act=2), 3),
@@ -120,7 +134,7 @@ for name, mk, count in OPS:
     fn, flops = mk()
     us = timeit(fn)
     total += us * count
-    print(f"{name:36s} {us:8.1f} us x{count}  {flops / us / 1e6:8.1f} TFLOP/s")
+    print(f"{name:52s} {us:8.1f} us x{count}  {flops / us / 1e6:8.1f} TFLOP/s")
     del fn
     torch.cuda.empty_cache()
 print(f"sum over one forward: {total:.0f} us")

@@ -62,6 +62,7 @@ SIGNATURES = {
     "tts_op_linear": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_int, vp, vp, vp,
                                 vp, vp, vp]),
     "tts_op_conv1d": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]),
+    "tts_op_ffn": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int, vp, vp]),
     "tts_op_attention": (C.c_int, [vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int,
                                    vp, vp, vp]),
 }

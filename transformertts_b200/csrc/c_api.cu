@@ -190,6 +190,17 @@ extern "C" int tts_op_conv1d(const void* x, const void* W, const float* bias, in
   return 0;
 }
 
+extern "C" int tts_op_ffn(const void* x, const void* w1, const float* b1, const void* w2, const float* b2,
+                          const float* ln_g, const float* ln_b, int M, void* out, void* stream) {
+  FfnArgs f;
+  f.x = (const bf16*)x; f.M = M;
+  f.w1 = (const bf16*)w1; f.b1 = b1; f.w2 = (const bf16*)w2; f.b2 = b2;
+  f.ln_g = ln_g; f.ln_b = ln_b; f.out = (bf16*)out;
+  if (!ffn_supports(f)) return fail("tts_op_ffn: pointers must be 16-byte aligned and x != out");
+  TRY(ffn_launch(f, (cudaStream_t)stream));
+  return 0;
+}
+
 extern "C" int tts_op_attention(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, int B, int Tq,
                                 int Tk, const int32_t* klen, int causal, void* out, float* probs, void* stream) {
   AttnArgs a;
@@ -231,6 +242,24 @@ static const char* proj(const bf16* A, int M, int K, const void* W, const float*
   return gemm_launch(g, s);
 }
 
+// x_out = LayerNorm(x + FFN(x)): the two-GEMM path through `hidden`, or one fused launch (ffn.cu) with TTS_FFN_FUSE=1.
+// Measured at cfg 2 the two are equal in isolation (86 vs 88 us per decoder layer) and the two-GEMM path is 1.4 %
+// faster inside the forward: at 128 rows per CTA the fused kernel has to stream all of W1 and W2 (1 MB) per tile and
+// its 7-slot ring cannot keep enough bytes in flight (profiles/README.md); it becomes the default once it runs on
+// CTA pairs (cta_group::2, 256 rows per weight pass).
+static const char* ffn_block(const bf16* x, int M, const TtsFfnW& w, const TtsLnW& ln, bf16* hidden, bf16* out,
+                             cudaStream_t s) {
+  static const bool no_fuse = getenv("TTS_FFN_FUSE") == nullptr;
+  FfnArgs f;
+  f.x = x; f.M = M;
+  f.w1 = (const bf16*)w.w1; f.b1 = w.b1; f.w2 = (const bf16*)w.w2; f.b2 = w.b2;
+  f.ln_g = ln.g; f.ln_b = ln.b; f.out = out;
+  if (!no_fuse && ffn_supports(f)) return ffn_launch(f, s);
+  const char* e = proj(x, M, kD, w.w1, w.b1, kF, ACT_RELU, hidden, s);
+  if (e) return e;
+  return proj_res_ln(hidden, M, kF, w.w2, w.b2, x, ln, out, s);
+}
+
 // emb -> EncoderPreNet -> PE -> 3 post-norm encoder layers (model/model.py:288-292 / 345-348).
 // Result (memory) is left in ws.e0.
 static const char* run_encoder(const TtsWeights* w, const int64_t* phoneme, int B, int Tp, bool masked, Workspace& ws,
@@ -258,8 +287,7 @@ static const char* run_encoder(const TtsWeights* w, const int64_t* phoneme, int 
     if ((e = run_attention(ws.qkv_e, 3 * kD, ws.qkv_e + kD, ws.qkv_e + 2 * kD, 3 * kD, ws.att_e, nullptr,
                            masked ? ws.ph_len : nullptr, B, Tp, Tp, 0, s))) return e;
     if ((e = proj_res_ln(ws.att_e, Np, kD, L.sa.w_out, L.sa.b_out, cur, L.ln1, nxt, s))) return e;
-    if ((e = proj(nxt, Np, kD, L.ffn.w1, L.ffn.b1, kF, ACT_RELU, ws.ffn_e, s))) return e;
-    if ((e = proj_res_ln(ws.ffn_e, Np, kF, L.ffn.w2, L.ffn.b2, nxt, L.ln2, cur, s))) return e;
+    if ((e = ffn_block(nxt, Np, L.ffn, L.ln2, ws.ffn_e, cur, s))) return e;
   }
   return cur == ws.e0 ? nullptr : "internal: encoder output buffer parity";
 }
@@ -380,8 +408,7 @@ extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const fl
     float* probs = (flags & TTS_FLAG_WANT_ALIGN) ? align + (size_t)l * B * kH * Tm * Tp : nullptr;
     TRY(run_attention(ws.cq, kD, ckv, ckv + kD, 2 * kD, ws.att_d, probs, ws.ph_len, B, Tm, Tp, 0, s));
     TRY(proj_res_ln(ws.att_d, Nm, kD, L.ca.w_out, L.ca.b_out, y, L.ln2, x, s));            // x = LN2
-    TRY(proj(x, Nm, kD, L.ffn.w1, L.ffn.b1, kF, ACT_RELU, ws.ffn_d, s));
-    TRY(proj_res_ln(ws.ffn_d, Nm, kF, L.ffn.w2, L.ffn.b2, x, L.ln3, y, s));                // y = LN3
+    TRY(ffn_block(x, Nm, L.ffn, L.ln3, ws.ffn_d, y, s));                                   // y = LN3
     bf16* t = x; x = y; y = t;
   }
   {                                                  // mel + stop heads (model/model.py:309,313)

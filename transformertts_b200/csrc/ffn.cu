@@ -1,0 +1,405 @@
+// Fused position-wise FFN block on tcgen05 / TMEM / TMA (sm_100a):
+//     y = LayerNorm(x + W2 relu(W1 x + b1) + b2),   d_model 256, hidden 1024
+// (torch/nn/modules/transformer.py:951-957, 980-982 as called by model/model.py:189-200 and model/layers.py:50).
+//
+// The two GEMMs of the block used to be two launches with the [rows][1024] bf16 hidden activation (105 MB at
+// cfg 2) written to and read back from L2/HBM in between.  Here one persistent CTA per SM owns a 128-row tile of x
+// and walks the hidden dimension in 8 chunks of 128: S = x W1[chunk]^T lands in TMEM, the epilogue warps turn it
+// into relu(S + b1) in bf16 straight into a swizzled smem tile H, and Y += H W2[:, chunk]^T accumulates in TMEM;
+// the hidden activation never leaves the SM.  The residual is added by identity MMAs from the resident x tile
+// (exact in fp32), LayerNorm runs in the final epilogue as in gemm2.cu.
+//   warp 0      TMA producer : x tile (4 k-blocks, resident for the tile), then W1 / W2 as a stream of uniform
+//                              [128 x 64] bf16 blocks through a 5-slot ring, in exactly the order the MMA warp eats them
+//   warp 1      MMA issuer   : GEMM1 of chunk c into S[c & 1] (N = 128, K = 256), then GEMM2 of chunk c-1 into the two
+//                              128-column halves of Y (K = 128), so the epilogue of chunk c-1 overlaps GEMM1 of chunk c
+//   warps 2..9  epilogue     : thread == (row, 64-column half of S): bias + ReLU -> bf16 H tile;  at the end of the tile
+//                              thread == (row, 128-column half of Y): + b2, LayerNorm, bf16, TMA store
+// TMEM: S0 | S1 | Y = 128 + 128 + 256 columns.  Shared memory: x 64 KB, H 32 KB, W ring 80 KB, identity 8 KB,
+// store slabs aliased onto H.
+#include <stdlib.h>
+#include <string.h>
+
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace tts {
+
+namespace ffn {
+constexpr int BM = 128, BK = 64, HC = 128, NHC = kF / HC;      // 8 hidden chunks
+constexpr int THREADS = 64 + 256;
+constexpr int BLK = 128 * BK * 2;                   // 16 KB: one [128 x 64] bf16 operand block
+constexpr int NSLOT = 7;
+constexpr int X_OFF = 0;                            // 4 blocks
+constexpr int H_OFF = X_OFF + 4 * BLK;              // 2 blocks
+constexpr int RING_OFF = H_OFF + 2 * BLK;
+constexpr int ID_OFF = RING_OFF + NSLOT * BLK;      // 64 x 64 identity, 8 KB
+constexpr int SLAB_OFF = H_OFF;                     // store slabs (2 halves x 2 buffers x 8 KB) reuse the H tile: H is
+                                                    // dead once the tile's last GEMM2 has completed (y_full)
+constexpr int CHUNK_BYTES = BM * 32 * 2;            // 8 KB
+constexpr int BAR_OFF = ID_OFF + 8192;
+constexpr int PAR_OFF = BAR_OFF + 256;              // b2[256] g[256] b[256] + LN partials (b1 is read through L1)
+constexpr int TOTAL = PAR_OFF + 3 * kD * 4 + 4096 + 1024;
+static_assert(TOTAL <= 232448, "shared memory plan exceeds 227 KB");
+
+struct Dev {
+  int M, m_tiles, n_pairs;                          // CTA pairs in the grid
+  const float* b1; const float* b2; const float* ln_g; const float* ln_b;
+};
+}  // namespace ffn
+
+using namespace ffn;
+
+__global__ void __launch_bounds__(THREADS, 1)
+ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
+           const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmO, const Dev p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  uint64_t* x_full = reinterpret_cast<uint64_t*>(smem + BAR_OFF);
+  uint64_t* x_empty = x_full + 1;
+  uint64_t* w_full = x_empty + 1;        // [NSLOT]
+  uint64_t* w_empty = w_full + NSLOT;    // [NSLOT]
+  uint64_t* s_full = w_empty + NSLOT;    // [2]
+  uint64_t* s_empty = s_full + 2;        // [2]  count 8: every epilogue warp holds its part of S in registers
+  uint64_t* h_full = s_empty + 2;        // [1]  count 8: H chunk written
+  uint64_t* h_empty = h_full + 1;        // [1]  GEMM2 has consumed H
+  uint64_t* y_full = h_empty + 1;        // [1]
+  uint64_t* y_empty = y_full + 1;        // [1]  count 8: Y drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(y_empty + 1);
+  float* s_b2 = reinterpret_cast<float*>(smem + PAR_OFF);
+  float* s_lng = s_b2 + kD;
+  float* s_lnb = s_lng + kD;
+  float2* s_stat = reinterpret_cast<float2*>(s_lnb + kD);      // [2 tile parities][2 halves][128 rows]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2); tma_prefetch_desc(&tmO);
+    mbar_init(x_full, 1); mbar_init(x_empty, 1);
+    for (int s = 0; s < NSLOT; ++s) { mbar_init(w_full + s, 1); mbar_init(w_empty + s, 2); }   // both CTAs release a slot
+    for (int i = 0; i < 2; ++i) { mbar_init(s_full + i, 1); mbar_init(s_empty + i, 8); }
+    mbar_init(h_full, 8); mbar_init(h_empty, 1); mbar_init(y_full, 1); mbar_init(y_empty, 8);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  if (warp >= 2) {
+    const int t = threadIdx.x - 64;
+    for (int i = t; i < kD; i += 256) { s_b2[i] = __ldg(p.b2 + i); s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
+    // 64x64 identity in the K-major SWIZZLE_128B operand layout (see gemm2.cu): residual by MMA
+    for (int ci = t; ci < 512; ci += 256) {
+      const int n = ci >> 3, c16 = ci & 7;
+      const uint32_t one = (n >> 3) == c16 ? ((n & 1) ? 0x3F800000u : 0x00003F80u) : 0u;   // bf16 1.0 at k == n
+      const int wi = (n & 7) >> 1;
+      *reinterpret_cast<uint4*>(smem + ID_OFF + n * 128 + ((c16 ^ (n & 7)) << 4)) =
+          make_uint4(wi == 0 ? one : 0u, wi == 1 ? one : 0u, wi == 2 ? one : 0u, wi == 3 ? one : 0u);
+    }
+    fence_proxy_async();
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                   // the peer's barriers are initialised before anything is multicast to them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  griddep_launch();
+  griddep_wait();
+  const uint32_t t_y = tmem_base + 256;
+  // The two CTAs of a cluster work on neighbouring row tiles in lock step and share the weight stream: every
+  // [128 x 64] block of W1 / W2 is fetched from L2 once, by one of them, and multicast into both rings.
+  const uint32_t crank = cluster_cta_rank();
+  const int pair = static_cast<int>(blockIdx.x >> 1);
+  auto tile_of = [&](int it) { return (it * p.n_pairs + pair) * 2 + static_cast<int>(crank); };
+  auto more = [&](int it) { return (it * p.n_pairs + pair) * 2 < p.m_tiles; };   // same verdict in both CTAs
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      uint32_t slot = 0, sph = 0;                       // ring position / phase
+      uint32_t blk = 0;                                 // blocks so far: even ones are fetched by rank 0, odd by rank 1
+      auto load_w = [&](const CUtensorMap* tm, int k0, int n0) {
+        mbar_wait(w_empty + slot, sph ^ 1);             // both CTAs are done with what the slot held
+        mbar_expect_tx(w_full + slot, BLK);
+        if ((blk & 1) == crank)
+          tma_load_3d_mc(smem + RING_OFF + slot * BLK, tm, w_full + slot, k0, n0, 0, (uint16_t)3);
+        ++blk;
+        if (++slot == NSLOT) { slot = 0; sph ^= 1; }
+      };
+      for (int it = 0; more(it); ++it) {
+        const int tile = tile_of(it);
+        mbar_wait(x_empty, (it & 1) ^ 1);
+        mbar_expect_tx(x_full, 4 * BLK);
+        for (int kb = 0; kb < 4; ++kb) tma_load_3d(smem + X_OFF + kb * BLK, &tmX, x_full, kb * BK, tile * BM, 0);
+        for (int hc = 0; hc <= NHC; ++hc) {
+          if (hc < NHC)
+            for (int kb = 0; kb < 4; ++kb) load_w(&tmW1, kb * BK, hc * HC);
+          if (hc >= 1)
+            for (int kb2 = 0; kb2 < 2; ++kb2)
+              for (int nh = 0; nh < 2; ++nh) load_w(&tmW2, (hc - 1) * HC + kb2 * BK, nh * 128);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, 128);
+      constexpr uint32_t idesc64 = umma_idesc_bf16(BM, 64);
+      uint32_t slot = 0, sph = 0;
+      uint32_t c = 0;                                   // hidden chunks issued so far (all tiles): S buffer / phases
+      uint32_t g2 = 0;                                  // GEMM2 chunks issued so far: h_full phase
+      auto next_slot = [&]() -> uint32_t {              // waits for the next W block, returns its smem address
+        mbar_wait(w_full + slot, sph);
+        tc_fence_after();
+        const uint32_t a = smem_u32(smem + RING_OFF + slot * BLK);
+        return a;
+      };
+      auto release_slot = [&]() {
+        tc_commit_mc(w_empty + slot, (uint16_t)3);      // this CTA's reads of the slot are done: tell both producers
+        if (++slot == NSLOT) { slot = 0; sph ^= 1; }
+      };
+      auto gemm2 = [&](int ch, int it) {               // Y += H(ch) W2[:, ch]^T
+        if (ch == 0) { mbar_wait(y_empty, (it & 1) ^ 1); }      // previous tile's Y has been drained
+        mbar_wait(h_full, g2 & 1);
+        tc_fence_after();
+        for (int kb2 = 0; kb2 < 2; ++kb2) {
+          const uint64_t dh = umma_desc_sw128(smem_u32(smem + H_OFF + kb2 * BLK));
+          for (int nh = 0; nh < 2; ++nh) {
+            const uint64_t dw = umma_desc_sw128(next_slot());
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              tc_mma_bf16(t_y + nh * 128, dh + 2 * k, dw + 2 * k, idesc, (ch > 0 || kb2 > 0 || k > 0) ? 1u : 0u);
+            release_slot();
+          }
+        }
+        tc_commit(h_empty);
+        ++g2;
+      };
+      for (int it = 0; more(it); ++it) {
+        mbar_wait(x_full, it & 1);
+        tc_fence_after();
+        for (int hc = 0; hc < NHC; ++hc, ++c) {
+          const uint32_t sb = c & 1;
+          mbar_wait(s_empty + sb, ((c >> 1) & 1) ^ 1);
+          tc_fence_after();
+          for (int kb = 0; kb < 4; ++kb) {
+            const uint64_t dx = umma_desc_sw128(smem_u32(smem + X_OFF + kb * BLK));
+            const uint64_t dw = umma_desc_sw128(next_slot());
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              tc_mma_bf16(tmem_base + sb * 128, dx + 2 * k, dw + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            release_slot();
+          }
+          tc_commit(s_full + sb);
+          if (hc >= 1) gemm2(hc - 1, it);
+        }
+        gemm2(NHC - 1, it);
+        // residual: Y[:, 64 kb .. 64 kb + 63] += x k-block * I
+        const uint64_t di = umma_desc_sw128(smem_u32(smem + ID_OFF));
+        for (int kb = 0; kb < 4; ++kb) {
+          const uint64_t dx = umma_desc_sw128(smem_u32(smem + X_OFF + kb * BLK));
+#pragma unroll
+          for (int k = 0; k < 4; ++k) tc_mma_bf16(t_y + kb * 64, dx + 2 * k, di + 2 * k, idesc64, 1u);
+        }
+        tc_commit(x_empty);
+        tc_commit(y_full);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------ epilogue warps
+    const int ew = warp - 2;
+    const int hf = ew >> 2;                             // column half: 64 of S's 128 columns, 128 of Y's 256
+    const int q = warp & 3;                             // TMEM lane quadrant
+    const int row = q * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    const uint32_t sw8 = static_cast<uint32_t>(row & 7);
+    const bool leader = (ew & 3) == 0 && lane == 0;
+    uint8_t* h_row = smem + H_OFF + hf * BLK + row * 128;       // this thread's 64 hidden columns = one 128-byte row
+    uint8_t* bufs = smem + SLAB_OFF + hf * (2 * CHUNK_BYTES);
+    const uint32_t sw4 = static_cast<uint32_t>((row >> 1) & 3);
+    uint8_t* my_row = bufs + row * 64;
+    uint32_t c = 0;                                     // hidden chunks processed so far (all tiles)
+    int kc = 0;                                         // output chunks staged so far (selects the slab buffer)
+    for (int it = 0; more(it); ++it) {
+      const int tile = tile_of(it);
+      // ---- hidden chunks: S -> relu(S + b1) -> bf16 H
+      for (int hc = 0; hc < NHC; ++hc, ++c) {
+        const uint32_t sb = c & 1;
+        mbar_wait(s_full + sb, (c >> 1) & 1);
+        tc_fence_after();
+        uint32_t r[64];
+        {
+          uint32_t (&r0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&r[0]);
+          uint32_t (&r1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&r[32]);
+          tmem_ld32(tmem_base + sb * 128 + hf * 64 + lane_off, r0);
+          tmem_ld32(tmem_base + sb * 128 + hf * 64 + 32 + lane_off, r1);
+          tmem_ld_wait();
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s_empty + sb);        // S is in registers: GEMM1 of chunk c+2 may overwrite it
+        const float4* b4 = reinterpret_cast<const float4*>(p.b1 + hc * HC + hf * 64);
+        uint32_t pk[32];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float4 bb = __ldg(b4 + j);
+          const float v0 = fmaxf(__uint_as_float(r[j * 4 + 0]) + bb.x, 0.f), v1 = fmaxf(__uint_as_float(r[j * 4 + 1]) + bb.y, 0.f);
+          const float v2 = fmaxf(__uint_as_float(r[j * 4 + 2]) + bb.z, 0.f), v3 = fmaxf(__uint_as_float(r[j * 4 + 3]) + bb.w, 0.f);
+          pk[j * 2] = pack_bf16(v0, v1);
+          pk[j * 2 + 1] = pack_bf16(v2, v3);
+        }
+        if (c > 0) {                                     // GEMM2 of the previous chunk has consumed H
+          mbar_wait(h_empty, (c - 1) & 1);
+        }
+        if (hc == 0 && it > 0) {                         // ... and the previous tile's TMA stores have left the slabs
+          if (leader) bulk_wait_read<0>();
+          named_bar_sync(1 + hf, 128);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(h_row + ((static_cast<uint32_t>(j) ^ sw8) << 4)) =
+              make_uint4(pk[j * 4 + 0], pk[j * 4 + 1], pk[j * 4 + 2], pk[j * 4 + 3]);
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(h_full);
+      }
+
+      // ---- Y = x + H W2^T (+ b2) -> LayerNorm -> bf16 -> TMA store; thread == (row, 128-column half)
+      mbar_wait(y_full, it & 1);
+      tc_fence_after();
+      const uint32_t tacc = t_y + hf * 128 + lane_off;
+      const float* sb2 = s_b2 + hf * 128;
+      float sum = 0.f, sq = 0.f;
+      for (int k = 0; k < 4; ++k) {
+        uint32_t r[32];
+        tmem_ld32(tacc + k * 32, r);
+        tmem_ld_wait();
+        const float4* b4 = reinterpret_cast<const float4*>(sb2 + k * 32);
+        float s4[4] = {0.f, 0.f, 0.f, 0.f}, q4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 bb = b4[j];
+          const float v0 = __uint_as_float(r[j * 4 + 0]) + bb.x, v1 = __uint_as_float(r[j * 4 + 1]) + bb.y;
+          const float v2 = __uint_as_float(r[j * 4 + 2]) + bb.z, v3 = __uint_as_float(r[j * 4 + 3]) + bb.w;
+          s4[0] += v0; s4[1] += v1; s4[2] += v2; s4[3] += v3;
+          q4[0] = fmaf(v0, v0, q4[0]); q4[1] = fmaf(v1, v1, q4[1]); q4[2] = fmaf(v2, v2, q4[2]); q4[3] = fmaf(v3, v3, q4[3]);
+        }
+        sum += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+        sq += (q4[0] + q4[1]) + (q4[2] + q4[3]);
+      }
+      float2* st = s_stat + (it & 1) * 256;
+      st[hf * 128 + row] = make_float2(sum, sq);
+      named_bar_sync(3, 256);                            // both halves of every row have published their partial sums
+      const float2 o = st[(hf ^ 1) * 128 + row];
+      sum += o.x; sq += o.y;
+      const float mean = sum * (1.f / kD);
+      const float rstd = rsqrtf(fmaxf(sq * (1.f / kD) - mean * mean, 0.f) + 1e-5f);
+      for (int k = 0; k < 4; ++k) {
+        uint32_t r[32];
+        tmem_ld32(tacc + k * 32, r);
+        tmem_ld_wait();
+        if (k == 3) {                                    // last read of Y: the next tile's GEMM2 may overwrite it
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(y_empty);
+        }
+        const int cc = hf * 4 + k;                       // 32-column chunk index within the 256 outputs
+        const float4* b4 = reinterpret_cast<const float4*>(sb2 + k * 32);
+        const float4* g4 = reinterpret_cast<const float4*>(s_lng + cc * 32);
+        const float4* l4 = reinterpret_cast<const float4*>(s_lnb + cc * 32);
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 g = g4[j], bb = l4[j], bi = b4[j];
+          v[j * 4 + 0] = (__uint_as_float(r[j * 4 + 0]) + bi.x - mean) * (rstd * g.x) + bb.x;
+          v[j * 4 + 1] = (__uint_as_float(r[j * 4 + 1]) + bi.y - mean) * (rstd * g.y) + bb.y;
+          v[j * 4 + 2] = (__uint_as_float(r[j * 4 + 2]) + bi.z - mean) * (rstd * g.z) + bb.z;
+          v[j * 4 + 3] = (__uint_as_float(r[j * 4 + 3]) + bi.w - mean) * (rstd * g.w) + bb.w;
+        }
+        const int bi2 = kc & 1;
+        uint8_t* ws = my_row + bi2 * CHUNK_BYTES;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 u;
+          u.x = pack_bf16(v[j * 8 + 0], v[j * 8 + 1]); u.y = pack_bf16(v[j * 8 + 2], v[j * 8 + 3]);
+          u.z = pack_bf16(v[j * 8 + 4], v[j * 8 + 5]); u.w = pack_bf16(v[j * 8 + 6], v[j * 8 + 7]);
+          *reinterpret_cast<uint4*>(ws + ((static_cast<uint32_t>(j) ^ sw4) << 4)) = u;
+        }
+        fence_proxy_async();
+        if (leader) bulk_wait_read<0>();                 // the other buffer (next chunk's) has been read out
+        named_bar_sync(1 + hf, 128);
+        if (leader) {
+          if (tile < p.m_tiles) tma_store_3d(&tmO, bufs + bi2 * CHUNK_BYTES, cc * 32, tile * BM, 0);
+          bulk_commit();
+        }
+        ++kc;
+      }
+    }
+    if (leader) bulk_wait<0>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                   // no multicast write or remote arrive may land in a CTA that has exited
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------ host side
+bool ffn_supports(const FfnArgs& a) {
+  auto al = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  return a.M > 0 && al(a.x) && al(a.w1) && al(a.w2) && al(a.out) && a.x != a.out;
+}
+
+const char* ffn_launch(const FfnArgs& a, cudaStream_t s) {
+  static bool attr_done = false;
+  static int sm_count = 0;
+  if (!attr_done) {
+    if (cudaFuncSetAttribute(ffn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TOTAL) != cudaSuccess)
+      return "cudaFuncSetAttribute(ffn) failed";
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
+      return "ffn: cannot query the SM count";
+    attr_done = true;
+  }
+  CUtensorMap tmX, tmW1, tmW2, tmO;
+  const char* e = make_tmap_3d(&tmX, a.x, kD, (uint64_t)a.M, 1, kD * 2, (uint64_t)a.M * kD * 2, BK, BM);
+  if (e) return e;
+  e = make_tmap_3d(&tmW1, a.w1, kD, kF, 1, kD * 2, (uint64_t)kF * kD * 2, BK, 128);
+  if (e) return e;
+  e = make_tmap_3d(&tmW2, a.w2, kF, kD, 1, kF * 2, (uint64_t)kF * kD * 2, BK, 128);
+  if (e) return e;
+  e = make_tmap_3d(&tmO, a.out, kD, (uint64_t)a.M, 1, kD * 2, (uint64_t)a.M * kD * 2, 32, BM, 64);
+  if (e) return e;
+  Dev p;
+  p.M = a.M; p.m_tiles = (a.M + BM - 1) / BM;
+  p.b1 = a.b1; p.b2 = a.b2; p.ln_g = a.ln_g; p.ln_b = a.ln_b;
+  // clusters that can be resident at once (GPC boundaries may leave single SMs unpaired): the tile walk is sized to it
+  static int max_pairs = 0;
+  if (max_pairs == 0) {
+    cudaLaunchConfig_t q = {};
+    q.gridDim = dim3(2 * (sm_count / 2)); q.blockDim = dim3(THREADS); q.dynamicSmemBytes = TOTAL;
+    cudaLaunchAttribute qa[1];
+    qa[0].id = cudaLaunchAttributeClusterDimension;
+    qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+    q.attrs = qa; q.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, ffn_kernel, &q) != cudaSuccess || n <= 0) { cudaGetLastError(); n = sm_count / 2; }
+    max_pairs = n < sm_count / 2 ? n : sm_count / 2;
+  }
+  const int pairs_needed = (p.m_tiles + 1) / 2;
+  p.n_pairs = pairs_needed < max_pairs ? pairs_needed : max_pairs;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * p.n_pairs); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = TOTAL; cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  const cudaError_t err = cudaLaunchKernelEx(&cfg, ffn_kernel, tmX, tmW1, tmW2, tmO, p);
+  note_launch();
+  return err == cudaSuccess ? nullptr : "ffn kernel launch failed";
+}
+
+}  // namespace tts

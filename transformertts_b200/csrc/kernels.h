@@ -49,6 +49,18 @@ const char* gemm_launch(const GemmArgs& a, cudaStream_t s);   // returns nullptr
 bool gemm2_supports(const GemmArgs& a);                        // persistent bf16-out kernel (gemm2.cu)
 const char* gemm2_launch(const GemmArgs& a, cudaStream_t s);
 
+// Fused FFN block: out = LayerNorm(x + W2 relu(W1 x + b1) + b2) over M rows of 256 channels (ffn.cu).
+// x, out bf16 [M][256] (distinct buffers), w1 bf16 [1024][256], w2 bf16 [256][1024], biases / LN fp32.
+struct FfnArgs {
+  const bf16* x; int M;
+  const bf16* w1; const float* b1;
+  const bf16* w2; const float* b2;
+  const float* ln_g; const float* ln_b;
+  bf16* out;
+};
+bool ffn_supports(const FfnArgs& a);
+const char* ffn_launch(const FfnArgs& a, cudaStream_t s);
+
 // Fused masked-softmax attention over packed projections.
 // Q rows: q[(b*Tq + i)*ldq + h*64 + d], K/V likewise with Tk, ldk/ldv.  Keys j >= klen[b] are masked
 // when klen != nullptr; causal masks j > i.  Q is expected pre-scaled by 1/sqrt(64).
