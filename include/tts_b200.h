@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define TTS_ABI_VERSION 1
+#define TTS_ABI_VERSION 2
 
 /* flags */
 #define TTS_FLAG_WANT_ALIGN 1 /* tts_forward: store cross-attention probabilities into `align` */
@@ -69,6 +69,10 @@ typedef struct TtsWeights {
   const void* head_w; const float* head_b;              /* bf16 [81][256]: rows 0-79 mel, row 80 stop */
   const void* post_w[5]; const float* post_b[5];        /* [256][5*128], 3x[256][5*256], [80][5*256] */
   const float* pe; float alpha; int32_t reserved1;      /* f32 [5000][256]; shared scalar alpha */
+  /* Cross-attention K/V projections of the three decoder layers stacked: bf16 [1536][256], rows 512 l + [0,256) = Wk of
+   * layer l, 512 l + [256,512) = Wv of layer l (copies of dec[l].ca.w_in rows 256-767), f32 [1536] likewise.  Lets
+   * tts_forward project the memory once for all layers.  May be NULL: the per-layer matrices are used then. */
+  const void* ckv_w; const float* ckv_b;
 } TtsWeights;
 
 int tts_abi_version(void);

@@ -43,6 +43,7 @@ class Weights(C.Structure):
         ("head_w", vp), ("head_b", fp),
         ("post_w", vp * 5), ("post_b", fp * 5),
         ("pe", fp), ("alpha", f32), ("reserved1", i32),
+        ("ckv_w", vp), ("ckv_b", fp),
     ]
 
 
@@ -82,7 +83,7 @@ def load():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)
             fn.restype, fn.argtypes = res, args
-        if lib.tts_abi_version() != 1:
+        if lib.tts_abi_version() != 2:
             raise RuntimeError("libtts_b200.so ABI version mismatch")
         _lib = lib
     return _lib

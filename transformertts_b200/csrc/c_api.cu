@@ -371,8 +371,13 @@ extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const fl
   }
   const char* enc_err = run_encoder(w, phoneme, B, Tp, (flags & TTS_FLAG_ENC_MASK) != 0, ws, se);
   const bf16* memory = ws.e0;
-  for (int l = 0; l < 3 && enc_err == nullptr; ++l)
-    enc_err = run_cross_kv(w, l, memory, Np, ws.ckv + (size_t)l * Np * 2 * kD, se);
+  const bool ckv_stacked = w->ckv_w != nullptr && w->ckv_b != nullptr;   // one [Np][1536] projection for all layers
+  if (ckv_stacked) {
+    if (enc_err == nullptr) enc_err = proj(memory, Np, kD, w->ckv_w, w->ckv_b, 6 * kD, ACT_NONE, ws.ckv, se);
+  } else {
+    for (int l = 0; l < 3 && enc_err == nullptr; ++l)
+      enc_err = run_cross_kv(w, l, memory, Np, ws.ckv + (size_t)l * Np * 2 * kD, se);
+  }
   if (side != nullptr && cudaEventRecord(side->join, se) != cudaSuccess) return fail("side stream join failed");
   struct JoinGuard {                                 // whatever path leaves this function, the caller's stream
     SideStream* side; cudaStream_t s; bool joined;   // ends up ordered after the encoder branch
@@ -404,9 +409,10 @@ extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const fl
       if (cudaStreamWaitEvent(s, side->join, 0) != cudaSuccess) return fail("side stream join failed");
       joined = true;
     }
-    const bf16* ckv = ws.ckv + (size_t)l * Np * 2 * kD;
+    const bf16* ckv = ckv_stacked ? ws.ckv + (size_t)l * 2 * kD : ws.ckv + (size_t)l * Np * 2 * kD;
+    const int ld_ckv = ckv_stacked ? 6 * kD : 2 * kD;
     float* probs = (flags & TTS_FLAG_WANT_ALIGN) ? align + (size_t)l * B * kH * Tm * Tp : nullptr;
-    TRY(run_attention(ws.cq, kD, ckv, ckv + kD, 2 * kD, ws.att_d, probs, ws.ph_len, B, Tm, Tp, 0, s));
+    TRY(run_attention(ws.cq, kD, ckv, ckv + kD, ld_ckv, ws.att_d, probs, ws.ph_len, B, Tm, Tp, 0, s));
     TRY(proj_res_ln(ws.att_d, Nm, kD, L.ca.w_out, L.ca.b_out, y, L.ln2, x, s));            // x = LN2
     TRY(ffn_block(x, Nm, L.ffn, L.ln3, ws.ffn_d, y, s));                                   // y = LN3
     bf16* t = x; x = y; y = t;

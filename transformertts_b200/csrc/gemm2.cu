@@ -28,7 +28,7 @@ constexpr int THREADS = 64 + 256;                  // producer warp, MMA warp, 8
 constexpr int A_BYTES = BM * BK * 2;               // 16 KB
 constexpr int B_BYTES = BN * BK * 2;               // 32 KB
 constexpr int CHUNK_BYTES = BM * 32 * 2;           // 128 rows x 32 bf16 columns = 8 KB staging buffer
-constexpr int MAX_N = 1024;
+constexpr int MAX_N = 2048;
 
 // Shared-memory plan.  WS ("W stationary", K <= 256, one tap): the CTA owns one 256-wide n-tile, keeps its whole
 // W slice (up to 4 k-blocks = 128 KB) resident and streams only A tiles, which cuts the L2 -> SM traffic per

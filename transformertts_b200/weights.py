@@ -111,6 +111,9 @@ class PackedWeights:
             w, b = fold_conv_bn(sd, f"postnet.layers.{3 * i}", 128 if i == 0 else D)
             assert w.shape[1] == KS * (128 if cin == N_MELS else D)
             s.post_w[i], s.post_b[i] = mat(w), vec(b)
+        # cross-attention K/V projections of all decoder layers stacked (rows 256-767 of each in_proj): one GEMM
+        s.ckv_w = mat(torch.cat([sd[f"decoder.layers.{l}.multihead_attn.in_proj_weight"][D:].float() for l in range(3)]))
+        s.ckv_b = vec(torch.cat([sd[f"decoder.layers.{l}.multihead_attn.in_proj_bias"][D:].float() for l in range(3)]))
         s.pe = vec(sd["pe.pe"])
         s.alpha = float(sd["pe.alpha"].reshape(-1)[0])
         self.struct = s
