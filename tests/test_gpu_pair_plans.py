@@ -1,0 +1,22 @@
+"""The persistent GEMM picks its plan per shape (single CTAs or cta_group::2 CTA pairs, gemm2.cu).  The library reads
+TTS_GEMM_PAIR once, so the other two settings are exercised in child processes: the operator parity tests and the
+golden-vector forward must pass with pairs forced on for every shape that allows them (2) and with pairs off (0)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.mark.parametrize("mode", ["0", "2"])
+def test_gemm_plans_under_forced_pair_mode(mode):
+    env = dict(os.environ, TTS_GEMM_PAIR=mode)
+    cmd = [sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu", "-p", "no:cacheprovider",
+           os.path.join(HERE, "test_gpu_ops.py"), os.path.join(HERE, "test_gpu_forward.py"),
+           "-k", "linear or conv1d or ffn or forward"]
+    r = subprocess.run(cmd, env=env, cwd=os.path.dirname(HERE), capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]

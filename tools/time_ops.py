@@ -18,12 +18,16 @@ st = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)
 P = _ext.ptr
 
 
+WARM = bool(os.environ.get("TTS_TIME_OPS_WARM"))   # skip the L2 flush: operands of the previous repetition stay cached
+
+
 def timeit(fn, reps=8):
     for _ in range(2):
         fn()
     tot = 0.0
     for _ in range(reps):
-        flush_buf.zero_()
+        if not WARM:
+            flush_buf.zero_()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(); fn(); b.record(); b.synchronize()
         tot += a.elapsed_time(b)

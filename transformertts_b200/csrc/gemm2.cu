@@ -36,12 +36,16 @@ constexpr int MAX_N = 2048;
 // F32 (fp32 heads / PostNet tail, N <= 128, never LN or WS): the first four epilogue warps stage 32-column fp32
 // chunks (128-byte rows, SWIZZLE_128B) plus an optional bf16 copy and publish both with TMA stores.
 constexpr int CHUNK32_BYTES = BM * 32 * 4;         // 16 KB
-template <bool LN, bool WS, bool F32 = false>
+// PAIR: two CTAs of a cluster share one 256 x 256 output tile pair (tcgen05 cta_group::2, M = 256).  Each CTA loads
+// its own 128 rows of A and only HALF of the W rows, so a streamed k-block is 32 KB instead of 48 KB and a resident W
+// slice 64 KB instead of 128 KB; the bytes saved become ring stages (the kernels are operand-delivery bound).
+template <bool LN, bool WS, bool F32 = false, bool PAIR = false>
 struct Plan {
-  static_assert(!F32 || (!LN && !WS), "the fp32-output plan streams W and has no LayerNorm");
-  static constexpr int W_BYTES = WS ? 4 * B_BYTES : 0;
-  static constexpr int ST = WS ? (LN ? 3 : 4) : 3;
-  static constexpr int STAGE_BYTES = WS ? A_BYTES : A_BYTES + B_BYTES;
+  static_assert(!F32 || (!LN && !WS && !PAIR), "the fp32-output plan streams W, has no LayerNorm and no CTA pairs");
+  static constexpr int WB = PAIR ? B_BYTES / 2 : B_BYTES;            // one W k-block as this CTA holds it
+  static constexpr int W_BYTES = WS ? 4 * WB : 0;
+  static constexpr int ST = PAIR ? (WS ? (LN ? 7 : 8) : 5) : (WS ? (LN ? 3 : 4) : 3);
+  static constexpr int STAGE_BYTES = WS ? A_BYTES : A_BYTES + WB;
   static constexpr int RING_OFF = W_BYTES;
   static constexpr int NBUF_H = WS ? 2 : 3;                         // staging buffers per epilogue half
   static constexpr int SLAB_OFF = RING_OFF + ST * STAGE_BYTES;
@@ -49,7 +53,7 @@ struct Plan {
   static constexpr int ID_OFF = SLAB_OFF + SLAB_BYTES;               // 64x64 bf16 identity (residual via MMA)
   static constexpr int BAR_OFF = ID_OFF + (LN ? 8192 : 0);
   static constexpr int PAR_OFF = BAR_OFF + 256;
-  static constexpr int NBIAS = WS ? BN : MAX_N;
+  static constexpr int NBIAS = (WS || LN) ? BN : MAX_N;
   static constexpr int TOTAL = PAR_OFF + (NBIAS + (LN ? 2 * BN : 0)) * 4 + (LN ? 4096 : 0) + 1024;  // + LN row partials
   static_assert(TOTAL <= 232448, "shared memory plan exceeds 227 KB");
 };
@@ -83,12 +87,12 @@ __device__ __forceinline__ void for_chunks4(uint32_t taddr, F&& f) {
   tmem_ld_wait(); f(3, rb);
 }
 
-template <bool LN, bool WS, bool F32>
+template <bool LN, bool WS, bool F32, bool PAIR>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
              const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const Dev p) {
   // tmO: bf16 output (may be unused when F32 && !has_bf16); tmR: bf16 residual (LN) or the fp32 output (F32)
-  using P = Plan<LN, WS, F32>;
+  using P = Plan<LN, WS, F32, PAIR>;
   constexpr int ST = P::ST;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
@@ -105,18 +109,28 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // tile walk: WS -> fixed n-tile per CTA, m-tiles strided; otherwise flat (m, n) list strided by the grid
-  const int ws_n = WS ? (int)(blockIdx.x % p.n_tiles) : 0;
-  const int ws_m0 = WS ? (int)(blockIdx.x / p.n_tiles) : 0;
-  const int ws_step = WS ? (int)(gridDim.x / p.n_tiles) : 0;
+  // tile walk: WS -> fixed n-tile per CTA, m-tiles strided; otherwise flat (m, n) list strided by the grid.
+  // PAIR: the walker is the cluster and a list entry is two consecutive m-tiles (rank 0 the even one, rank 1 the odd
+  // one; an odd tile past the end loads zeros and stores nothing), so both CTAs run the same number of iterations.
+  const int rank = PAIR ? (int)cluster_cta_rank() : 0;
+  const int wid = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;           // walker id
+  const int nwalk = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int m_units = PAIR ? (p.m_tiles + 1) >> 1 : p.m_tiles;
+  const int ws_n = WS ? wid % p.n_tiles : 0;
+  const int ws_m0 = WS ? wid / p.n_tiles : 0;
+  const int ws_step = WS ? nwalk / p.n_tiles : 0;
   auto tile_at = [&](int i, int& m_tile, int& n_tile) -> bool {
+    int mu; bool ok;
     if (WS) {
-      m_tile = ws_m0 + i * ws_step; n_tile = ws_n;
-      return m_tile < p.m_tiles;
+      mu = ws_m0 + i * ws_step; n_tile = ws_n;
+      ok = mu < m_units;
+    } else {
+      const int unit = wid + i * nwalk;
+      n_tile = unit % p.n_tiles; mu = unit / p.n_tiles;
+      ok = unit < m_units * p.n_tiles;
     }
-    const int tile = blockIdx.x + i * gridDim.x;
-    n_tile = tile % p.n_tiles; m_tile = tile / p.n_tiles;
-    return tile < p.total_tiles;
+    m_tile = PAIR ? 2 * mu + rank : mu;
+    return ok;
   };
 
   if (warp == 0 && lane == 0) {
@@ -125,13 +139,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tma_prefetch_desc(&tmO);
     if (LN) tma_prefetch_desc(&tmR);
     for (int s = 0; s < ST; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, PAIR ? 16 : 8); }   // PAIR: the epilogue warps of both CTAs
     mbar_init(w_full, 1);
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, 512);
-    tmem_relinquish();
+    if (PAIR) { tmem_alloc_cg2(tmem_slot, 512); tmem_relinquish_cg2(); }
+    else { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
   }
   if (warp >= 2) {
     const int nb0 = WS ? ws_n * BN : 0;
@@ -141,18 +155,20 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       for (int i = threadIdx.x - 64; i < BN; i += 256) { s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
       // 64x64 identity in the K-major SWIZZLE_128B operand layout: the residual tile is added to the accumulator
       // by four extra N=64 MMAs (x * I, exact in fp32), so it rides the prefetched A pipeline instead of the epilogue
-      for (int ci = threadIdx.x - 64; ci < 512; ci += 256) {
-        const int n = ci >> 3, c16 = ci & 7;
+      // (PAIR: B is split by rows over the two CTAs, this one holds identity rows 32*rank .. 32*rank+31)
+      for (int ci = threadIdx.x - 64; ci < (PAIR ? 256 : 512); ci += 256) {
+        const int nl = ci >> 3, c16 = ci & 7;
+        const int n = nl + (PAIR ? 32 * rank : 0);
         const uint32_t one = (n >> 3) == c16 ? ((n & 1) ? 0x3F800000u : 0x00003F80u) : 0u;   // bf16 1.0 at k == n
         const int wi = (n & 7) >> 1;
-        *reinterpret_cast<uint4*>(smem + P::ID_OFF + n * 128 + ((c16 ^ (n & 7)) << 4)) =
+        *reinterpret_cast<uint4*>(smem + P::ID_OFF + nl * 128 + ((c16 ^ (nl & 7)) << 4)) =
             make_uint4(wi == 0 ? one : 0u, wi == 1 ? one : 0u, wi == 2 ? one : 0u, wi == 3 ? one : 0u);
       }
       fence_proxy_async();
     }
   }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all(); else __syncthreads();      // PAIR: the peer's barriers are initialised before anyone signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   griddep_launch();
@@ -161,9 +177,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
+      // PAIR: both CTAs load their own halves; every byte is counted on rank 0's barrier (the MMA issuer waits there),
+      // which rank 0 arms with the bytes of both
+      const int nload = PAIR ? 2 : 1;
+      auto load = [&](void* dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2) {
+        if (PAIR) tma_load_3d_cg2(dst, tm, mapa_u32(smem_u32(bar), 0), c0, c1, c2);
+        else tma_load_3d(dst, tm, bar, c0, c1, c2);
+      };
       if (WS) {
-        mbar_expect_tx(w_full, p.num_kb * B_BYTES);
-        for (int kb = 0; kb < p.num_kb; ++kb) tma_load_3d(smem + kb * B_BYTES, &tmW, w_full, kb * BK, ws_n * BN, 0);
+        if (rank == 0) mbar_expect_tx(w_full, p.num_kb * P::WB * nload);
+        for (int kb = 0; kb < p.num_kb; ++kb)
+          load(smem + kb * P::WB, &tmW, w_full, kb * BK, ws_n * BN + rank * (BN / 2), 0);
       }
       int s = 0; uint32_t ph = 0;
       int m_tile, n_tile;
@@ -175,12 +199,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           if (kb < p.num_kb) {
             const int tap = kb / p.kc_per_tap;
             const int kc = kb - tap * p.kc_per_tap;
-            mbar_expect_tx(full + s, F32 ? A_BYTES + p.w_stage_bytes : P::STAGE_BYTES);
-            tma_load_3d(sa, &tmA, full + s, kc * BK, t0 + tap + p.tap_off, b);
-            if (!WS) tma_load_3d(sa + A_BYTES, &tmW, full + s, kb * BK, n0, 0);
+            if (rank == 0) mbar_expect_tx(full + s, (F32 ? A_BYTES + p.w_stage_bytes : P::STAGE_BYTES) * nload);
+            load(sa, &tmA, full + s, kc * BK, t0 + tap + p.tap_off, b);
+            if (!WS) load(sa + A_BYTES, &tmW, full + s, kb * BK, n0 + rank * (BN / 2), 0);
           } else {                                   // residual k-block: 64 columns of the residual tile
-            mbar_expect_tx(full + s, A_BYTES);
-            tma_load_3d(sa, &tmR, full + s, (kb - p.num_kb) * BK, t0, b);
+            if (rank == 0) mbar_expect_tx(full + s, A_BYTES * nload);
+            load(sa, &tmR, full + s, (kb - p.num_kb) * BK, t0, b);
           }
           if (++s == ST) { s = 0; ph ^= 1; }
         }
@@ -189,8 +213,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0) {
-      const uint32_t idesc = F32 ? umma_idesc_bf16(BM, p.n_mma) : umma_idesc_bf16(BM, BN);
+    if (lane == 0 && rank == 0) {
+      constexpr int MM = PAIR ? 2 * BM : BM;         // MMA rows: the pair's 256 rows, 128 in each CTA's TMEM
+      const uint32_t idesc = F32 ? umma_idesc_bf16(BM, p.n_mma) : umma_idesc_bf16(MM, BN);
+      auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t id, uint32_t acc) {
+        if (PAIR) tc_mma_bf16_cg2(d, da, db, id, acc); else tc_mma_bf16(d, da, db, id, acc);
+      };
+      auto commit = [&](uint64_t* bar) { if (PAIR) tc_commit_cg2(bar, 3); else tc_commit(bar); };
       int s = 0; uint32_t ph = 0;
       int m_tile, n_tile;
       if (WS) { mbar_wait(w_full, 0); tc_fence_after(); }
@@ -207,19 +236,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           const uint32_t sa = smem_u32(smem + P::RING_OFF + s * P::STAGE_BYTES);
           const uint64_t da = umma_desc_sw128(sa);
           if (kb < p.num_kb) {
-            const uint64_t db = umma_desc_sw128(WS ? smem_u32(smem + kb * B_BYTES) : sa + A_BYTES);
+            const uint64_t db = umma_desc_sw128(WS ? smem_u32(smem + kb * P::WB) : sa + A_BYTES);
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k)
-              tc_mma_bf16(tacc, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+              mma(tacc, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
           } else {                                   // acc[:, 64r .. 64r+63] += residual k-block * I
-            constexpr uint32_t idesc64 = umma_idesc_bf16(BM, 64);
+            constexpr uint32_t idesc64 = umma_idesc_bf16(MM, 64);
             const uint64_t di = umma_desc_sw128(smem_u32(smem + P::ID_OFF));
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k)
-              tc_mma_bf16(tacc + (kb - p.num_kb) * 64, da + 2 * k, di + 2 * k, idesc64, 1u);
+              mma(tacc + (kb - p.num_kb) * 64, da + 2 * k, di + 2 * k, idesc64, 1u);
           }
-          tc_commit(empty + s);
-          if (kb == total_kb - 1) tc_commit(acc_full + buf);
+          commit(empty + s);
+          if (kb == total_kb - 1) commit(acc_full + buf);
           if (++s == ST) { s = 0; ph ^= 1; }
         }
       }
@@ -384,7 +413,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (k == 3) {                                // last read of this TMEM buffer: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(acc_empty + buf);
+          if (lane == 0) {
+            if (PAIR) mbar_arrive_cluster(mapa_u32(smem_u32(acc_empty + buf), 0));   // the issuer lives in rank 0
+            else mbar_arrive(acc_empty + buf);
+          }
         }
         float v[32];
         const float4* sb = reinterpret_cast<const float4*>(sbias_h + k * 32);
@@ -447,20 +479,22 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }  // !F32
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 512);
+  if (PAIR) cluster_sync_all(); else __syncthreads();      // PAIR: neither CTA retires while the other may still signal it
+  if (warp == 1) {
+    if (PAIR) tmem_dealloc_cg2(tmem_base, 512); else tmem_dealloc(tmem_base, 512);
+  }
 }
 
 // ------------------------------------------------------------------ host side
 static int g_sm_count = 0;
 
-template <bool LN, bool WS, bool F32 = false>
+template <bool LN, bool WS, bool F32 = false, bool PAIR = false>
 static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
                            const CUtensorMap& tmR, const Dev& p, cudaStream_t s) {
-  using P = Plan<LN, WS, F32>;
+  using P = Plan<LN, WS, F32, PAIR>;
   static bool attr_done = false;
   if (!attr_done) {
-    if (cudaFuncSetAttribute(gemm2_kernel<LN, WS, F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::TOTAL) !=
+    if (cudaFuncSetAttribute(gemm2_kernel<LN, WS, F32, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::TOTAL) !=
         cudaSuccess)
       return "cudaFuncSetAttribute(gemm2) failed";
     attr_done = true;
@@ -471,12 +505,23 @@ static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const
         cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || g_sm_count <= 0)
       return "gemm2: cannot query the SM count";
   }
-  int grid = p.total_tiles < g_sm_count ? p.total_tiles : g_sm_count;
-  if (WS) grid = (grid / p.n_tiles) * p.n_tiles;          // every CTA owns one n-tile
-  const cudaError_t err = launch_pdl(gemm2_kernel<LN, WS, F32>, dim3(grid), dim3(THREADS), P::TOTAL, s, tmA, tmW, tmO, tmR, p);
+  cudaError_t err;
+  if (PAIR) {
+    const int units = ((p.m_tiles + 1) / 2) * p.n_tiles;   // list entries: pairs of m-tiles
+    int pairs = units < g_sm_count / 2 ? units : g_sm_count / 2;
+    if (WS) pairs = (pairs / p.n_tiles) * p.n_tiles;      // every pair owns one n-tile
+    err = launch_pdl_pairs(gemm2_kernel<LN, WS, F32, PAIR>, dim3(2 * pairs), dim3(THREADS), P::TOTAL, s, tmA, tmW, tmO, tmR, p);
+  } else {
+    int grid = p.total_tiles < g_sm_count ? p.total_tiles : g_sm_count;
+    if (WS) grid = (grid / p.n_tiles) * p.n_tiles;        // every CTA owns one n-tile
+    err = launch_pdl(gemm2_kernel<LN, WS, F32, PAIR>, dim3(grid), dim3(THREADS), P::TOTAL, s, tmA, tmW, tmO, tmR, p);
+  }
   note_launch();
   return err == cudaSuccess ? nullptr : "gemm2 kernel launch failed";
 }
+
+// W-stationary pairs: every pair owns one n-tile, so there must be at least n_tiles pairs (74 on a B200)
+static bool g_pairs_ok(int n_tiles) { return n_tiles <= 64; }
 
 static bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
 
@@ -545,7 +590,16 @@ const char* gemm2_launch(const GemmArgs& a, cudaStream_t s) {
   p.total_tiles = p.m_tiles * p.n_tiles;
   static const bool no_ws = getenv("TTS_GEMM_NO_WS") != nullptr;
   const bool ws = !no_ws && a.taps == 1 && p.num_kb <= 4;
-  e = make_tmap_3d(&tmW, a.W, (uint64_t)ktot, (uint64_t)a.N, 1, (uint64_t)ktot * 2, (uint64_t)ktot * 2 * a.N, BK, BN);
+  // CTA pairs (tcgen05 cta_group::2): measured faster for the long-K streaming plans (FFN2 + LN -12 %, PostNet
+  // conv -5 %) and slower for the W-stationary ones (their steady state is HBM-write bound and the pair adds
+  // cross-CTA hand-offs), so the default takes pairs only when W streams with K >= 1024.
+  // TTS_GEMM_PAIR=0: never, =2: whenever the shape allows (keeps the W-stationary pair plans under test).
+  static const char* pair_env = getenv("TTS_GEMM_PAIR");
+  const int pair_mode = pair_env ? atoi(pair_env) : 1;
+  const bool pair_ok = p.m_tiles >= 2 * (ws ? p.n_tiles : 1) && (!ws || g_pairs_ok(p.n_tiles));
+  const bool pair = pair_ok && (pair_mode >= 2 || (pair_mode == 1 && !ws && p.num_kb >= 16));
+  e = make_tmap_3d(&tmW, a.W, (uint64_t)ktot, (uint64_t)a.N, 1, (uint64_t)ktot * 2, (uint64_t)ktot * 2 * a.N, BK,
+                   pair ? BN / 2 : BN);
   if (e) return e;
   e = make_tmap_3d(&tmO, a.out_bf16, (uint64_t)a.N, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_bf16 * 2,
                    (uint64_t)a.T * a.ld_bf16 * 2, 32, BM, 64);
@@ -554,8 +608,12 @@ const char* gemm2_launch(const GemmArgs& a, cudaStream_t s) {
     e = make_tmap_3d(&tmR, a.residual, (uint64_t)a.N, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_res * 2,
                      (uint64_t)a.T * a.ld_res * 2, 64, BM);
     if (e) return e;
+    if (pair) return ws ? launch2<true, true, false, true>(tmA, tmW, tmO, tmR, p, s)
+                        : launch2<true, false, false, true>(tmA, tmW, tmO, tmR, p, s);
     return ws ? launch2<true, true>(tmA, tmW, tmO, tmR, p, s) : launch2<true, false>(tmA, tmW, tmO, tmR, p, s);
   }
+  if (pair) return ws ? launch2<false, true, false, true>(tmA, tmW, tmO, tmO, p, s)
+                      : launch2<false, false, false, true>(tmA, tmW, tmO, tmO, p, s);
   return ws ? launch2<false, true>(tmA, tmW, tmO, tmO, p, s) : launch2<false, false>(tmA, tmW, tmO, tmO, p, s);
 }
 
