@@ -242,14 +242,13 @@ static const char* proj(const bf16* A, int M, int K, const void* W, const float*
   return gemm_launch(g, s);
 }
 
-// x_out = LayerNorm(x + FFN(x)): the two-GEMM path through `hidden`, or one fused launch (ffn.cu) with TTS_FFN_FUSE=1.
-// Measured at cfg 2 the two are equal in isolation (86 vs 88 us per decoder layer) and the two-GEMM path is 1.4 %
-// faster inside the forward: at 128 rows per CTA the fused kernel has to stream all of W1 and W2 (1 MB) per tile and
-// its 7-slot ring cannot keep enough bytes in flight (profiles/README.md); it becomes the default once it runs on
-// CTA pairs (cta_group::2, 256 rows per weight pass).
+// x_out = LayerNorm(x + FFN(x)): one fused launch on CTA pairs (ffn.cu; the hidden activation stays in tensor
+// memory), or with TTS_FFN_FUSE=0 the two-GEMM path through `hidden`.  Measured at cfg 2: 64.5 us against
+// 37.6 + 46.1 us per decoder layer in isolation, 1.193 against 1.235 ms for the whole forward (profiles/README.md).
 static const char* ffn_block(const bf16* x, int M, const TtsFfnW& w, const TtsLnW& ln, bf16* hidden, bf16* out,
                              cudaStream_t s) {
-  static const bool no_fuse = getenv("TTS_FFN_FUSE") == nullptr;
+  static const char* fuse_env = getenv("TTS_FFN_FUSE");
+  static const bool no_fuse = fuse_env != nullptr && fuse_env[0] == '0';
   FfnArgs f;
   f.x = x; f.M = M;
   f.w1 = (const bf16*)w.w1; f.b1 = w.b1; f.w2 = (const bf16*)w.w2; f.b2 = w.b2;

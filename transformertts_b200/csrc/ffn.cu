@@ -2,20 +2,27 @@
 //     y = LayerNorm(x + W2 relu(W1 x + b1) + b2),   d_model 256, hidden 1024
 // (torch/nn/modules/transformer.py:951-957, 980-982 as called by model/model.py:189-200 and model/layers.py:50).
 //
-// The two GEMMs of the block used to be two launches with the [rows][1024] bf16 hidden activation (105 MB at
-// cfg 2) written to and read back from L2/HBM in between.  Here one persistent CTA per SM owns a 128-row tile of x
-// and walks the hidden dimension in 8 chunks of 128: S = x W1[chunk]^T lands in TMEM, the epilogue warps turn it
-// into relu(S + b1) in bf16 straight into a swizzled smem tile H, and Y += H W2[:, chunk]^T accumulates in TMEM;
-// the hidden activation never leaves the SM.  The residual is added by identity MMAs from the resident x tile
-// (exact in fp32), LayerNorm runs in the final epilogue as in gemm2.cu.
-//   warp 0      TMA producer : x tile (4 k-blocks, resident for the tile), then W1 / W2 as a stream of uniform
-//                              [128 x 64] bf16 blocks through a 5-slot ring, in exactly the order the MMA warp eats them
-//   warp 1      MMA issuer   : GEMM1 of chunk c into S[c & 1] (N = 128, K = 256), then GEMM2 of chunk c-1 into the two
-//                              128-column halves of Y (K = 128), so the epilogue of chunk c-1 overlaps GEMM1 of chunk c
-//   warps 2..9  epilogue     : thread == (row, 64-column half of S): bias + ReLU -> bf16 H tile;  at the end of the tile
-//                              thread == (row, 128-column half of Y): + b2, LayerNorm, bf16, TMA store
-// TMEM: S0 | S1 | Y = 128 + 128 + 256 columns.  Shared memory: x 64 KB, H 32 KB, W ring 80 KB, identity 8 KB,
-// store slabs aliased onto H.
+// The two GEMMs of the block are otherwise two launches with the [rows][1024] bf16 hidden activation (105 MB at
+// cfg 2) written to and read back from L2/HBM in between.  Here a CTA PAIR (cluster of two, tcgen05 cta_group::2)
+// owns 256 rows of x, 128 per CTA, and walks the hidden dimension in 8 chunks of 128: S = x W1[chunk]^T lands in
+// TMEM, the epilogue warps turn it into H = relu(S + b1) in bf16 and store it back over the S columns it came from
+// (tcgen05.st), and Y += H W2[:, chunk]^T accumulates in TMEM with H as the tensor-memory A operand; the hidden
+// activation never leaves the SM, not even into shared memory.  With 256-row MMAs each CTA
+// holds only HALF of the rows of every W block, so the whole of W1/W2 (1 MB) is streamed once per 256 rows and each
+// SM ingests 512 KB of it instead of 1 MB per 128 rows.  The residual is added by identity MMAs from the resident
+// x tile (exact in fp32), LayerNorm runs in the final epilogue as in gemm2.cu.
+//   warp 0      TMA producer : (both CTAs) own x tile (4 k-blocks, resident for the tile), then its halves of W1 / W2
+//                              as a stream of 16 KB slots through a 7-slot ring, in the order the MMA warp eats them;
+//                              all bytes are counted on rank 0's barriers
+//   warp 1      MMA issuer   : (rank 0 only) GEMM1 of chunk c into S[c & 1] (256 x 128, K = 256), then GEMM2 of chunk
+//                              c-1 into Y (256 x 256, K = 128), so the epilogue of chunk c-1 overlaps GEMM1 of chunk c;
+//                              completions are multicast to the barriers of both CTAs
+//   warps 2..9  epilogue     : (both CTAs) thread == (row, 64-column half of S): bias + ReLU -> bf16 -> TMEM;  at the end
+//                              of the tile thread == (row, 128-column half of Y): + b2, LayerNorm, bf16, TMA store;
+//                              hand-backs arrive on the CTA's own barriers, rank 1's are forwarded by its idle warp 1
+// TMEM per CTA: S0 | S1 | Y = 128 + 128 + 256 columns; H(c) lives in columns 0..31 and 64..95 of S[c & 1] and is
+// protected by issue order alone: GEMM1 of chunk c+2, which overwrites it, is issued after GEMM2 of chunk c.
+// Shared memory per CTA: x 64 KB, store slabs 32 KB, W ring 112 KB, identity 4 KB, b1 4 KB.
 #include <stdlib.h>
 #include <string.h>
 
@@ -30,14 +37,14 @@ constexpr int THREADS = 64 + 256;
 constexpr int BLK = 128 * BK * 2;                   // 16 KB: one [128 x 64] bf16 operand block
 constexpr int NSLOT = 7;
 constexpr int X_OFF = 0;                            // 4 blocks
-constexpr int H_OFF = X_OFF + 4 * BLK;              // 2 blocks
+constexpr int H_OFF = X_OFF + 4 * BLK;              // store slabs: 2 halves x 2 buffers x 8 KB
 constexpr int RING_OFF = H_OFF + 2 * BLK;
-constexpr int ID_OFF = RING_OFF + NSLOT * BLK;      // 64 x 64 identity, 8 KB
-constexpr int SLAB_OFF = H_OFF;                     // store slabs (2 halves x 2 buffers x 8 KB) reuse the H tile: H is
-                                                    // dead once the tile's last GEMM2 has completed (y_full)
+constexpr int ID_OFF = RING_OFF + NSLOT * BLK;      // this CTA's 32 rows of the 64 x 64 identity, 4 KB
+constexpr int B1_OFF = ID_OFF + 4096;               // b1[1024] fp32, 4 KB
+constexpr int SLAB_OFF = H_OFF;
 constexpr int CHUNK_BYTES = BM * 32 * 2;            // 8 KB
-constexpr int BAR_OFF = ID_OFF + 8192;
-constexpr int PAR_OFF = BAR_OFF + 256;              // b2[256] g[256] b[256] + LN partials (b1 is read through L1)
+constexpr int BAR_OFF = B1_OFF + 4096;
+constexpr int PAR_OFF = BAR_OFF + 256;              // b2[256] g[256] b[256] + LN partials
 constexpr int TOTAL = PAR_OFF + 3 * kD * 4 + 4096 + 1024;
 static_assert(TOTAL <= 232448, "shared memory plan exceeds 227 KB");
 
@@ -59,55 +66,60 @@ ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
   uint64_t* w_full = x_empty + 1;        // [NSLOT]
   uint64_t* w_empty = w_full + NSLOT;    // [NSLOT]
   uint64_t* s_full = w_empty + NSLOT;    // [2]
-  uint64_t* s_empty = s_full + 2;        // [2]  count 8: every epilogue warp holds its part of S in registers
-  uint64_t* h_full = s_empty + 2;        // [1]  count 8: H chunk written
-  uint64_t* h_empty = h_full + 1;        // [1]  GEMM2 has consumed H
-  uint64_t* y_full = h_empty + 1;        // [1]
+  uint64_t* h_full = s_full + 2;         // [2]  every epilogue warp has stored its part of H(c) over S(c).  One barrier per S
+                                         //      buffer: S(c+1) may be ready before the slowest warp has finished chunk c, and a
+                                         //      fast warp's arrival for c+1 must not be counted into chunk c's phase
+  uint64_t* y_full = h_full + 2;         // [1]
   uint64_t* y_empty = y_full + 1;        // [1]  count 8: Y drained
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(y_empty + 1);
   float* s_b2 = reinterpret_cast<float*>(smem + PAR_OFF);
   float* s_lng = s_b2 + kD;
   float* s_lnb = s_lng + kD;
   float2* s_stat = reinterpret_cast<float2*>(s_lnb + kD);      // [2 tile parities][2 halves][128 rows]
+  float* s_b1 = reinterpret_cast<float*>(smem + B1_OFF);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t crank = cluster_cta_rank();
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2); tma_prefetch_desc(&tmO);
     mbar_init(x_full, 1); mbar_init(x_empty, 1);
-    for (int s = 0; s < NSLOT; ++s) { mbar_init(w_full + s, 1); mbar_init(w_empty + s, 2); }   // both CTAs release a slot
-    for (int i = 0; i < 2; ++i) { mbar_init(s_full + i, 1); mbar_init(s_empty + i, 8); }
-    mbar_init(h_full, 8); mbar_init(h_empty, 1); mbar_init(y_full, 1); mbar_init(y_empty, 8);
+    for (int s = 0; s < NSLOT; ++s) { mbar_init(w_full + s, 1); mbar_init(w_empty + s, 1); }
+    // hand-backs to the issuer: the 8 epilogue warps arrive on their OWN CTA's barrier (a cluster-scope arrive costs
+    // ~1000 cycles); rank 1's otherwise idle warp 1 waits there and forwards one arrive to rank 0 (hence 8 + 1)
+    const uint32_t nb = crank == 0 ? 9 : 8;
+    for (int i = 0; i < 2; ++i) mbar_init(s_full + i, 1);
+    mbar_init(h_full, nb); mbar_init(h_full + 1, nb); mbar_init(y_full, 1); mbar_init(y_empty, nb);
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, 512);
-    tmem_relinquish();
+    tmem_alloc_cg2(tmem_slot, 512);
+    tmem_relinquish_cg2();
   }
   if (warp >= 2) {
     const int t = threadIdx.x - 64;
     for (int i = t; i < kD; i += 256) { s_b2[i] = __ldg(p.b2 + i); s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
-    // 64x64 identity in the K-major SWIZZLE_128B operand layout (see gemm2.cu): residual by MMA
-    for (int ci = t; ci < 512; ci += 256) {
-      const int n = ci >> 3, c16 = ci & 7;
+    for (int i = t; i < kF; i += 256) s_b1[i] = __ldg(p.b1 + i);
+    // rows 32*rank .. 32*rank+31 of the 64x64 identity in the K-major SWIZZLE_128B operand layout (see gemm2.cu):
+    // residual by MMA, the B operand of a pair MMA is split by rows over the two CTAs
+    for (int ci = t; ci < 256; ci += 256) {
+      const int nl = ci >> 3, c16 = ci & 7;
+      const int n = nl + 32 * static_cast<int>(crank);
       const uint32_t one = (n >> 3) == c16 ? ((n & 1) ? 0x3F800000u : 0x00003F80u) : 0u;   // bf16 1.0 at k == n
       const int wi = (n & 7) >> 1;
-      *reinterpret_cast<uint4*>(smem + ID_OFF + n * 128 + ((c16 ^ (n & 7)) << 4)) =
+      *reinterpret_cast<uint4*>(smem + ID_OFF + nl * 128 + ((c16 ^ (nl & 7)) << 4)) =
           make_uint4(wi == 0 ? one : 0u, wi == 1 ? one : 0u, wi == 2 ? one : 0u, wi == 3 ? one : 0u);
     }
     fence_proxy_async();
   }
   tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();                   // the peer's barriers are initialised before anything is multicast to them
+  cluster_sync_all();                   // the peer's barriers are initialised before anything is signalled on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   griddep_launch();
   griddep_wait();
   const uint32_t t_y = tmem_base + 256;
-  // The two CTAs of a cluster work on neighbouring row tiles in lock step and share the weight stream: every
-  // [128 x 64] block of W1 / W2 is fetched from L2 once, by one of them, and multicast into both rings.
-  const uint32_t crank = cluster_cta_rank();
+  // The two CTAs of a cluster work on neighbouring row tiles in lock step: one 256-row MMA stream issued by rank 0.
   const int pair = static_cast<int>(blockIdx.x >> 1);
   auto tile_of = [&](int it) { return (it * p.n_pairs + pair) * 2 + static_cast<int>(crank); };
   auto more = [&](int it) { return (it * p.n_pairs + pair) * 2 < p.m_tiles; };   // same verdict in both CTAs
@@ -116,35 +128,44 @@ ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
     // ------------------------------------------------------------ TMA producer
     if (lane == 0) {
       uint32_t slot = 0, sph = 0;                       // ring position / phase
-      uint32_t blk = 0;                                 // blocks so far: even ones are fetched by rank 0, odd by rank 1
-      auto load_w = [&](const CUtensorMap* tm, int k0, int n0) {
-        mbar_wait(w_empty + slot, sph ^ 1);             // both CTAs are done with what the slot held
-        mbar_expect_tx(w_full + slot, BLK);
-        if ((blk & 1) == crank)
-          tma_load_3d_mc(smem + RING_OFF + slot * BLK, tm, w_full + slot, k0, n0, 0, (uint16_t)3);
-        ++blk;
-        if (++slot == NSLOT) { slot = 0; sph ^= 1; }
+      const int r = static_cast<int>(crank);
+      auto bar0 = [&](uint64_t* bar) { return mapa_u32(smem_u32(bar), 0); };     // the barrier of that name in rank 0
+      // one ring slot = 16 KB of this CTA's half: two [64 x 64] blocks of W1 or one [128 x 64] block of W2
+      auto next = [&]() -> uint8_t* {
+        mbar_wait(w_empty + slot, sph ^ 1);             // the MMAs that read what the slot held have completed
+        if (r == 0) mbar_expect_tx(w_full + slot, 2 * BLK);
+        return smem + RING_OFF + slot * BLK;
       };
+      auto advance = [&]() { if (++slot == NSLOT) { slot = 0; sph ^= 1; } };
       for (int it = 0; more(it); ++it) {
         const int tile = tile_of(it);
         mbar_wait(x_empty, (it & 1) ^ 1);
-        mbar_expect_tx(x_full, 4 * BLK);
-        for (int kb = 0; kb < 4; ++kb) tma_load_3d(smem + X_OFF + kb * BLK, &tmX, x_full, kb * BK, tile * BM, 0);
+        if (r == 0) mbar_expect_tx(x_full, 2 * 4 * BLK);
+        for (int kb = 0; kb < 4; ++kb) tma_load_3d_cg2(smem + X_OFF + kb * BLK, &tmX, bar0(x_full), kb * BK, tile * BM, 0);
         for (int hc = 0; hc <= NHC; ++hc) {
           if (hc < NHC)
-            for (int kb = 0; kb < 4; ++kb) load_w(&tmW1, kb * BK, hc * HC);
+            for (int h2 = 0; h2 < 2; ++h2) {            // W1 rows hc*128 + 64 r .. + 63, k-blocks 2 h2 and 2 h2 + 1
+              uint8_t* dst = next();
+              tma_load_3d_cg2(dst, &tmW1, bar0(w_full + slot), (2 * h2) * BK, hc * HC + r * 64, 0);
+              tma_load_3d_cg2(dst + BLK / 2, &tmW1, bar0(w_full + slot), (2 * h2 + 1) * BK, hc * HC + r * 64, 0);
+              advance();
+            }
           if (hc >= 1)
-            for (int kb2 = 0; kb2 < 2; ++kb2)
-              for (int nh = 0; nh < 2; ++nh) load_w(&tmW2, (hc - 1) * HC + kb2 * BK, nh * 128);
+            for (int kb2 = 0; kb2 < 2; ++kb2) {         // W2 rows 128 r .. + 127, hidden columns of chunk hc - 1
+              uint8_t* dst = next();
+              tma_load_3d_cg2(dst, &tmW2, bar0(w_full + slot), (hc - 1) * HC + kb2 * BK, r * 128, 0);
+              advance();
+            }
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, 128);
-      constexpr uint32_t idesc64 = umma_idesc_bf16(BM, 64);
+    if (lane == 0 && crank == 0) {
+      constexpr uint32_t idesc1 = umma_idesc_bf16(2 * BM, 128);     // S chunk: 256 rows (128 per CTA) x 128
+      constexpr uint32_t idesc2 = umma_idesc_bf16(2 * BM, 256);     // Y: 256 x 256
+      constexpr uint32_t idesc64 = umma_idesc_bf16(2 * BM, 64);
       uint32_t slot = 0, sph = 0;
       uint32_t c = 0;                                   // hidden chunks issued so far (all tiles): S buffer / phases
       uint32_t g2 = 0;                                  // GEMM2 chunks issued so far: h_full phase
@@ -155,54 +176,71 @@ ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
         return a;
       };
       auto release_slot = [&]() {
-        tc_commit_mc(w_empty + slot, (uint16_t)3);      // this CTA's reads of the slot are done: tell both producers
+        tc_commit_cg2(w_empty + slot, (uint16_t)3);     // the pair's reads of the slot are done: tell both producers
         if (++slot == NSLOT) { slot = 0; sph ^= 1; }
       };
       auto gemm2 = [&](int ch, int it) {               // Y += H(ch) W2[:, ch]^T
-        if (ch == 0) { mbar_wait(y_empty, (it & 1) ^ 1); }      // previous tile's Y has been drained
-        mbar_wait(h_full, g2 & 1);
-        tc_fence_after();
-        for (int kb2 = 0; kb2 < 2; ++kb2) {
-          const uint64_t dh = umma_desc_sw128(smem_u32(smem + H_OFF + kb2 * BLK));
-          for (int nh = 0; nh < 2; ++nh) {
-            const uint64_t dw = umma_desc_sw128(next_slot());
+        if (ch == 0) {
+          mbar_wait(y_empty, (it & 1) ^ 1);             // previous tile's Y has been drained
+          tc_fence_after();
+          // Y starts as the residual: Y[:, 64 kb .. 64 kb + 63] = x k-block * I (exact in fp32)
+          const uint64_t di = umma_desc_sw128(smem_u32(smem + ID_OFF));
+          for (int kb = 0; kb < 4; ++kb) {
+            const uint64_t dx = umma_desc_sw128(smem_u32(smem + X_OFF + kb * BLK));
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              tc_mma_bf16(t_y + nh * 128, dh + 2 * k, dw + 2 * k, idesc, (ch > 0 || kb2 > 0 || k > 0) ? 1u : 0u);
-            release_slot();
+            for (int k = 0; k < 4; ++k) tc_mma_bf16_cg2(t_y + kb * 64, dx + 2 * k, di + 2 * k, idesc64, k > 0 ? 1u : 0u);
           }
         }
-        tc_commit(h_empty);
+        mbar_wait(h_full + (g2 & 1), (g2 >> 1) & 1);
+        tc_fence_after();
+        const uint32_t t_h = tmem_base + (g2 & 1) * 128;            // H(ch) sits where S(ch) was: S buffer = chunk parity
+        for (int kb2 = 0; kb2 < 2; ++kb2) {
+          const uint64_t dw = umma_desc_sw128(next_slot());
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            tc_mma_bf16_cg2_ts(t_y, t_h + kb2 * 64 + k * 8, dw + 2 * k, idesc2, 1u);
+          release_slot();
+        }
         ++g2;
       };
       for (int it = 0; more(it); ++it) {
         mbar_wait(x_full, it & 1);
         tc_fence_after();
         for (int hc = 0; hc < NHC; ++hc, ++c) {
-          const uint32_t sb = c & 1;
-          mbar_wait(s_empty + sb, ((c >> 1) & 1) ^ 1);
-          tc_fence_after();
-          for (int kb = 0; kb < 4; ++kb) {
-            const uint64_t dx = umma_desc_sw128(smem_u32(smem + X_OFF + kb * BLK));
-            const uint64_t dw = umma_desc_sw128(next_slot());
+          const uint32_t sb = c & 1;             // S[sb] held H(c-2): its GEMM2 was issued before, the pipe runs in order
+          for (int h2 = 0; h2 < 2; ++h2) {
+            const uint32_t wa = next_slot();
+            for (int kk = 0; kk < 2; ++kk) {
+              const int kb = 2 * h2 + kk;
+              const uint64_t dx = umma_desc_sw128(smem_u32(smem + X_OFF + kb * BLK));
+              const uint64_t dw = umma_desc_sw128(wa + kk * (BLK / 2));
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              tc_mma_bf16(tmem_base + sb * 128, dx + 2 * k, dw + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+              for (int k = 0; k < 4; ++k)
+                tc_mma_bf16_cg2(tmem_base + sb * 128, dx + 2 * k, dw + 2 * k, idesc1, (kb > 0 || k > 0) ? 1u : 0u);
+            }
             release_slot();
           }
-          tc_commit(s_full + sb);
+          tc_commit_cg2(s_full + sb, (uint16_t)3);
+          if (hc == NHC - 1) tc_commit_cg2(x_empty, (uint16_t)3);   // last read of the x tile (the residual went in with chunk 0):
+                                                                   // the next tile's x loads overlap the last two GEMM2s
           if (hc >= 1) gemm2(hc - 1, it);
         }
         gemm2(NHC - 1, it);
-        // residual: Y[:, 64 kb .. 64 kb + 63] += x k-block * I
-        const uint64_t di = umma_desc_sw128(smem_u32(smem + ID_OFF));
-        for (int kb = 0; kb < 4; ++kb) {
-          const uint64_t dx = umma_desc_sw128(smem_u32(smem + X_OFF + kb * BLK));
-#pragma unroll
-          for (int k = 0; k < 4; ++k) tc_mma_bf16(t_y + kb * 64, dx + 2 * k, di + 2 * k, idesc64, 1u);
+        tc_commit_cg2(y_full, (uint16_t)3);
+      }
+    }
+    if (lane == 0 && crank == 1) {
+      // ---------------------------------------------------------- relay: rank 1's hand-backs, forwarded in the order
+      // the epilogue produces them (per chunk: H stored; per tile: Y drained)
+      const uint32_t r_h_full = mapa_u32(smem_u32(h_full), 0), r_y_empty = mapa_u32(smem_u32(y_empty), 0);
+      uint32_t c = 0;
+      for (int it = 0; more(it); ++it) {
+        for (int hc = 0; hc < NHC; ++hc, ++c) {
+          mbar_wait(h_full + (c & 1), (c >> 1) & 1);
+          mbar_arrive_cluster(r_h_full + (c & 1) * 8);
         }
-        tc_commit(x_empty);
-        tc_commit(y_full);
+        mbar_wait(y_empty, it & 1);
+        mbar_arrive_cluster(r_y_empty);
       }
     }
     __syncwarp();
@@ -213,9 +251,7 @@ ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
     const int q = warp & 3;                             // TMEM lane quadrant
     const int row = q * 32 + lane;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
-    const uint32_t sw8 = static_cast<uint32_t>(row & 7);
     const bool leader = (ew & 3) == 0 && lane == 0;
-    uint8_t* h_row = smem + H_OFF + hf * BLK + row * 128;       // this thread's 64 hidden columns = one 128-byte row
     uint8_t* bufs = smem + SLAB_OFF + hf * (2 * CHUNK_BYTES);
     const uint32_t sw4 = static_cast<uint32_t>((row >> 1) & 3);
     uint8_t* my_row = bufs + row * 64;
@@ -228,41 +264,31 @@ ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
         const uint32_t sb = c & 1;
         mbar_wait(s_full + sb, (c >> 1) & 1);
         tc_fence_after();
-        uint32_t r[64];
-        {
-          uint32_t (&r0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&r[0]);
-          uint32_t (&r1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&r[32]);
-          tmem_ld32(tmem_base + sb * 128 + hf * 64 + lane_off, r0);
-          tmem_ld32(tmem_base + sb * 128 + hf * 64 + 32 + lane_off, r1);
-          tmem_ld_wait();
-        }
+        uint32_t r0[32], r1[32];
+        tmem_ld32(tmem_base + sb * 128 + hf * 64 + lane_off, r0);
+        tmem_ld_wait();
+        tmem_ld32(tmem_base + sb * 128 + hf * 64 + 32 + lane_off, r1);     // in flight while the first half is processed
+        const float4* b4 = reinterpret_cast<const float4*>(s_b1 + hc * HC + hf * 64);
+        uint32_t pk[32];
+        auto half = [&](const uint32_t (&r)[32], int o) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 bb = b4[o * 8 + j];
+            const float v0 = fmaxf(__uint_as_float(r[j * 4 + 0]) + bb.x, 0.f), v1 = fmaxf(__uint_as_float(r[j * 4 + 1]) + bb.y, 0.f);
+            const float v2 = fmaxf(__uint_as_float(r[j * 4 + 2]) + bb.z, 0.f), v3 = fmaxf(__uint_as_float(r[j * 4 + 3]) + bb.w, 0.f);
+            pk[o * 16 + j * 2] = pack_bf16(v0, v1);
+            pk[o * 16 + j * 2 + 1] = pack_bf16(v2, v3);
+          }
+        };
+        half(r0, 0);
+        tmem_ld_wait();
+        half(r1, 1);
+        // 64 bf16 of this row = 32 packed columns, stored over the first half of the 64 S columns they came from
+        tmem_st32(tmem_base + sb * 128 + hf * 64 + lane_off, pk);
+        tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(s_empty + sb);        // S is in registers: GEMM1 of chunk c+2 may overwrite it
-        const float4* b4 = reinterpret_cast<const float4*>(p.b1 + hc * HC + hf * 64);
-        uint32_t pk[32];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float4 bb = __ldg(b4 + j);
-          const float v0 = fmaxf(__uint_as_float(r[j * 4 + 0]) + bb.x, 0.f), v1 = fmaxf(__uint_as_float(r[j * 4 + 1]) + bb.y, 0.f);
-          const float v2 = fmaxf(__uint_as_float(r[j * 4 + 2]) + bb.z, 0.f), v3 = fmaxf(__uint_as_float(r[j * 4 + 3]) + bb.w, 0.f);
-          pk[j * 2] = pack_bf16(v0, v1);
-          pk[j * 2 + 1] = pack_bf16(v2, v3);
-        }
-        if (c > 0) {                                     // GEMM2 of the previous chunk has consumed H
-          mbar_wait(h_empty, (c - 1) & 1);
-        }
-        if (hc == 0 && it > 0) {                         // ... and the previous tile's TMA stores have left the slabs
-          if (leader) bulk_wait_read<0>();
-          named_bar_sync(1 + hf, 128);
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<uint4*>(h_row + ((static_cast<uint32_t>(j) ^ sw8) << 4)) =
-              make_uint4(pk[j * 4 + 0], pk[j * 4 + 1], pk[j * 4 + 2], pk[j * 4 + 3]);
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(h_full);
+        if (lane == 0) mbar_arrive(h_full + sb);
       }
 
       // ---- Y = x + H W2^T (+ b2) -> LayerNorm -> bf16 -> TMA store; thread == (row, 128-column half)
@@ -339,9 +365,8 @@ ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
     if (leader) bulk_wait<0>();
   }
   tc_fence_before();
-  __syncthreads();
-  cluster_sync_all();                   // no multicast write or remote arrive may land in a CTA that has exited
-  if (warp == 1) tmem_dealloc(tmem_base, 512);
+  cluster_sync_all();                   // no commit or remote arrive may land in a CTA that has exited
+  if (warp == 1) tmem_dealloc_cg2(tmem_base, 512);
 }
 
 // ------------------------------------------------------------------ host side
@@ -365,7 +390,7 @@ const char* ffn_launch(const FfnArgs& a, cudaStream_t s) {
   CUtensorMap tmX, tmW1, tmW2, tmO;
   const char* e = make_tmap_3d(&tmX, a.x, kD, (uint64_t)a.M, 1, kD * 2, (uint64_t)a.M * kD * 2, BK, BM);
   if (e) return e;
-  e = make_tmap_3d(&tmW1, a.w1, kD, kF, 1, kD * 2, (uint64_t)kF * kD * 2, BK, 128);
+  e = make_tmap_3d(&tmW1, a.w1, kD, kF, 1, kD * 2, (uint64_t)kF * kD * 2, BK, 64);     // this CTA's half of a hidden chunk
   if (e) return e;
   e = make_tmap_3d(&tmW2, a.w2, kF, kD, 1, kF * 2, (uint64_t)kF * kD * 2, BK, 128);
   if (e) return e;

@@ -139,7 +139,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tma_prefetch_desc(&tmO);
     if (LN) tma_prefetch_desc(&tmR);
     for (int s = 0; s < ST; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, PAIR ? 16 : 8); }   // PAIR: the epilogue warps of both CTAs
+    // PAIR: the epilogue warps hand the accumulator back on their own CTA's barrier (a cluster-scope arrive costs
+    // ~1000 cycles); rank 1's otherwise idle warp 1 waits there and forwards one arrive to the issuer in rank 0
+    for (int i = 0; i < 2; ++i) { mbar_init(acc_full + i, 1); mbar_init(acc_empty + i, (PAIR && rank == 0) ? 9 : 8); }
     mbar_init(w_full, 1);
     fence_mbar_init();
   }
@@ -251,6 +253,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           if (kb == total_kb - 1) commit(acc_full + buf);
           if (++s == ST) { s = 0; ph ^= 1; }
         }
+      }
+    }
+    if (PAIR && lane == 0 && rank == 1) {
+      // relay: forward rank 1's accumulator hand-backs to the issuer
+      const uint32_t remote = mapa_u32(smem_u32(acc_empty), 0);
+      int m_tile, n_tile;
+      for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
+        const int buf = it & 1;
+        mbar_wait(acc_empty + buf, (it >> 1) & 1);
+        mbar_arrive_cluster(remote + buf * 8);
       }
     }
     __syncwarp();
@@ -413,10 +425,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (k == 3) {                                // last read of this TMEM buffer: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) {
-            if (PAIR) mbar_arrive_cluster(mapa_u32(smem_u32(acc_empty + buf), 0));   // the issuer lives in rank 0
-            else mbar_arrive(acc_empty + buf);
-          }
+          if (lane == 0) mbar_arrive(acc_empty + buf);
         }
         float v[32];
         const float4* sb = reinterpret_cast<const float4*>(sbias_h + k * 32);
@@ -590,14 +599,16 @@ const char* gemm2_launch(const GemmArgs& a, cudaStream_t s) {
   p.total_tiles = p.m_tiles * p.n_tiles;
   static const bool no_ws = getenv("TTS_GEMM_NO_WS") != nullptr;
   const bool ws = !no_ws && a.taps == 1 && p.num_kb <= 4;
-  // CTA pairs (tcgen05 cta_group::2): measured faster for the long-K streaming plans (FFN2 + LN -12 %, PostNet
-  // conv -5 %) and slower for the W-stationary ones (their steady state is HBM-write bound and the pair adds
-  // cross-CTA hand-offs), so the default takes pairs only when W streams with K >= 1024.
-  // TTS_GEMM_PAIR=0: never, =2: whenever the shape allows (keeps the W-stationary pair plans under test).
+  // CTA pairs (tcgen05 cta_group::2): measured faster for the long-K streaming plans (FFN2 + LN -10 %, PostNet
+  // conv -6 %) and for the W-stationary LayerNorm plan (out-projection + LN -5 %: its ring grows from 3 to 7 stages),
+  // equal or slower for the other W-stationary shapes (HBM-write bound in the steady state), so the default takes
+  // pairs when W streams with K >= 1024 or when the plan is W-stationary with LayerNorm.
+  // TTS_GEMM_PAIR=0: never, =2: whenever the shape allows (keeps every pair plan under test).
   static const char* pair_env = getenv("TTS_GEMM_PAIR");
   const int pair_mode = pair_env ? atoi(pair_env) : 1;
   const bool pair_ok = p.m_tiles >= 2 * (ws ? p.n_tiles : 1) && (!ws || g_pairs_ok(p.n_tiles));
-  const bool pair = pair_ok && (pair_mode >= 2 || (pair_mode == 1 && !ws && p.num_kb >= 16));
+  const bool pair_pick = ws ? a.residual != nullptr : p.num_kb >= 16;
+  const bool pair = pair_ok && (pair_mode >= 2 || (pair_mode == 1 && pair_pick));
   e = make_tmap_3d(&tmW, a.W, (uint64_t)ktot, (uint64_t)a.N, 1, (uint64_t)ktot * 2, (uint64_t)ktot * 2 * a.N, BK,
                    pair ? BN / 2 : BN);
   if (e) return e;

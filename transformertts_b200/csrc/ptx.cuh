@@ -214,6 +214,18 @@ __device__ __forceinline__ void tc_mma_bf16_cg2(uint32_t tmem_d, uint64_t desc_a
       : "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// same with the A operand in tensor memory: each CTA's 128 rows x 16 bf16 are 8 columns of its own TMEM at tmem_a
+// (lane == row, two K-neighbours packed per 32-bit column, the lower K in the low half)
+__device__ __forceinline__ void tc_mma_bf16_cg2_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                                   uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n"
+      :
+      : "r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // one thread: D[tmem] (+)= A[smem] * B[smem]^T, bf16 x bf16 -> fp32
 __device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                             uint32_t accumulate) {
