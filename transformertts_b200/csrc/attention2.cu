@@ -15,9 +15,11 @@
 //   warp 0      TMA producer : Q tile per item (two buffers), K/V tiles into a 3-stage ring (SWIZZLE_128B)
 //   warp 1      MMA issuer   : S = Q K^T (128x64x64) into one of two TMEM buffers, O += P V (128x64x64,
 //                              V consumed MN-major straight from its [key][dim] tile), fp32 accumulators in TMEM
-//   warps 2..5  softmax      : thread == query row: tcgen05.ld S -> masks -> online max/sum (exp2) -> bf16 P into a
-//                              swizzled smem tile (the A operand of P V); O is rescaled in TMEM only when the
-//                              running max grew by more than 2^8 (lazy rescale), normalised once at the end
+//   warps 2..5  softmax      : thread == query row: tcgen05.ld S -> masks -> online max/sum (exp2) -> bf16 P stored
+//                              back over the first 32 of the 64 S columns it came from (tcgen05.st): P V takes its A
+//                              operand from tensor memory, so P never touches shared memory and tile j+1's P does not
+//                              wait for P V of tile j; O is rescaled in TMEM only when the running max grew by more
+//                              than 2^8 (lazy rescale), normalised once at the end
 // With probs != nullptr a second sweep recomputes S per tile and stores exp2(s - m) / l through a padded smem
 // transpose so every row leaves as 128-byte coalesced segments.
 #include "kernels.h"
@@ -142,7 +144,6 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
     if (lane == 0) {
-      const uint64_t dp = umma_desc_sw128(smem_u32(smem + P_OFF));
       // S cursor: runs two tiles ahead of the P V cursor through the same flattened (item, tile) stream
       Walker wS; Item iS;
       bool haveS = wS.next(p, iS);
@@ -180,8 +181,8 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
             const int s = GP % ST;
             const uint64_t dv = umma_desc_sw128(smem_u32(smem + KV_OFF + s * STAGE_BYTES + KV_TILE));
 #pragma unroll
-            for (int k = 0; k < 4; ++k)                  // 16 keys per step: P advances 32 B, V advances 16 rows
-              tc_mma_bf16(t_o, dp + 2 * k, dv + 128 * k, idesc_pv(), (j > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < 4; ++k)                  // 16 keys per step: P advances 8 TMEM columns, V 16 rows
+              tc_mma_bf16_ts(t_o, t_s0 + (GP & 1) * 64 + 8 * k, dv + 128 * k, idesc_pv(), (j > 0 || k > 0) ? 1u : 0u);
             tc_commit(kv_empty + s);
             tc_commit(pv_done);
           }
@@ -195,8 +196,6 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
     const int q = warp & 3;
     const int row = q * 32 + lane;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
-    const uint32_t sw = static_cast<uint32_t>(row & 7);
-    uint8_t* p_row = smem + P_OFF + row * 128;
     Walker w; Item it;
     uint32_t G = 0;                                      // tiles consumed so far (all items): S buffer / phase
     uint32_t np = 0;                                     // P V products completed before this item: pv_done phase
@@ -252,10 +251,10 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
           pk[e] = pack_bf16(p0, p1);
         }
         l += (sm[0] + sm[1]) + (sm[2] + sm[3]);
-        if (j > 0) {                                              // P V of tile j-1 must be done with P and O
-          mbar_wait(pv_done, (np + j - 1) & 1);
+        if (j > 0 && __any_sync(0xffffffffu, grew)) {             // rescale: P V of tile j-1 must be done with O
+          mbar_wait(pv_done, (np + j - 1) & 1);                   // (s_full of this tile implies P V of tile j-2)
           tc_fence_after();
-          if (__any_sync(0xffffffffu, grew)) {
+          {
             uint32_t o[32];
 #pragma unroll
             for (int hlf = 0; hlf < 2; ++hlf) {
@@ -268,17 +267,19 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
             tmem_st_wait();
           }
         }
-#pragma unroll
-        for (int c = 0; c < 8; ++c)
-          *reinterpret_cast<uint4*>(p_row + ((static_cast<uint32_t>(c) ^ sw) << 4)) =
-              make_uint4(pk[c * 4 + 0], pk[c * 4 + 1], pk[c * 4 + 2], pk[c * 4 + 3]);
-        fence_proxy_async();
+        // P(j) over S(j): this thread's 64 scores are in registers, the next S into this buffer (tile j+2) is issued
+        // after P V of tile j and the tensor pipe runs in order
+        tmem_st32(t_s0 + (G & 1) * 64 + lane_off, pk);
+        tmem_st_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(p_full + (G & 1));
       }
 
       // ---- O = O / l -> bf16 -> global (one 128-byte row segment per thread)
+      // a parity wait may only be one phase ahead of the barrier: s_full of the last tile implied P V of tile n1-3,
+      // so wait for n1-2 and then n1-1
+      if (n1 >= 2) mbar_wait(pv_done, (np + n1 - 2) & 1);
       mbar_wait(pv_done, (np + n1 - 1) & 1);
       tc_fence_after();
       np += n1;
