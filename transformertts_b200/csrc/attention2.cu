@@ -93,8 +93,10 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
   uint64_t* kv_empty = kv_full + ST;     // [ST]
   uint64_t* s_full = kv_empty + ST;      // [2]
   uint64_t* p_full = s_full + 2;         // [2]  softmax is done with S buffer (and P / O are ready)
-  uint64_t* pv_done = p_full + 2;        // [1]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 1);
+  uint64_t* pv_done = p_full + 2;        // [2]  P V number g (counted over the CTA's whole walk) commits to pv_done[g & 1]:
+                                         //      the softmax warps skip most of these waits, and a parity wait is only
+                                         //      meaningful while the barrier is at most one phase away from the waiter
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -103,7 +105,7 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
     for (int i = 0; i < 2; ++i) { mbar_init(q_full + i, 1); mbar_init(q_empty + i, 1); }
     for (int s = 0; s < ST; ++s) { mbar_init(kv_full + s, 1); mbar_init(kv_empty + s, 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(s_full + i, 1); mbar_init(p_full + i, 4); }
-    mbar_init(pv_done, 1);
+    mbar_init(pv_done, 1); mbar_init(pv_done + 1, 1);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -173,6 +175,7 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
       issue_next_s();
       Walker wP; Item iP;
       uint32_t GP = 0;
+      uint32_t NP = 0;                                  // P V products issued so far
       while (wP.next(p, iP)) {
         for (int j = 0; j < iP.n_all; ++j, ++GP) {
           mbar_wait(p_full + (GP & 1), (GP >> 1) & 1);   // softmax consumed this S (and wrote P, rescaled O)
@@ -184,7 +187,8 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
             for (int k = 0; k < 4; ++k)                  // 16 keys per step: P advances 8 TMEM columns, V 16 rows
               tc_mma_bf16_ts(t_o, t_s0 + (GP & 1) * 64 + 8 * k, dv + 128 * k, idesc_pv(), (j > 0 || k > 0) ? 1u : 0u);
             tc_commit(kv_empty + s);
-            tc_commit(pv_done);
+            tc_commit(pv_done + (NP & 1));
+            ++NP;
           }
           issue_next_s();
         }
@@ -252,7 +256,8 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
         }
         l += (sm[0] + sm[1]) + (sm[2] + sm[3]);
         if (j > 0 && __any_sync(0xffffffffu, grew)) {             // rescale: P V of tile j-1 must be done with O
-          mbar_wait(pv_done, (np + j - 1) & 1);                   // (s_full of this tile implies P V of tile j-2)
+          const uint32_t g = np + j - 1;                          // (s_full of this tile implies P V of tile j-2,
+          mbar_wait(pv_done + (g & 1), (g >> 1) & 1);             //  so pv_done[g & 1] is at most one phase behind)
           tc_fence_after();
           {
             uint32_t o[32];
@@ -277,10 +282,10 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
       }
 
       // ---- O = O / l -> bf16 -> global (one 128-byte row segment per thread)
-      // a parity wait may only be one phase ahead of the barrier: s_full of the last tile implied P V of tile n1-3,
-      // so wait for n1-2 and then n1-1
-      if (n1 >= 2) mbar_wait(pv_done, (np + n1 - 2) & 1);
-      mbar_wait(pv_done, (np + n1 - 1) & 1);
+      {
+        const uint32_t g = np + n1 - 1;                           // last P V of the item (tile n1-3 is known complete)
+        mbar_wait(pv_done + (g & 1), (g >> 1) & 1);
+      }
       tc_fence_after();
       np += n1;
       const float inv = l > 0.f ? 1.f / l : 0.f;
