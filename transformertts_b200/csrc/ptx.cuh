@@ -57,13 +57,15 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 // Bounded wait: a protocol bug must surface as a trapped kernel (an error the host reports),
-// never as a hung GPU box.  ~2^26 try_wait probes is seconds of wall time.
+// never as a hung GPU box.  The bound is wall time (~2 s of SM clock), because one try_wait probe may itself
+// suspend the thread for a hardware-chosen interval.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
 #pragma unroll 1
-  for (uint32_t i = 0; i < (1u << 26); ++i) {
-    if (mbar_try_wait(bar, parity)) return;
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) __trap();
   }
-  __trap();
 }
 
 // ---------------------------------------------------------------- TMA
