@@ -43,10 +43,14 @@ __host__ __device__ inline int smem_total(int NT) { return smem_main(NT) + 64 + 
 
 using namespace a3;
 
+// The probabilities are written once and not read again by the forward: store them with an L2 evict-first policy so
+// 123 MB of alignments per layer do not push the 26 MB activations the next kernels read out of L2.
 __device__ __forceinline__ void bulk_store_1d(void* gdst, const void* smem_src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
                :
-               : "l"(reinterpret_cast<uint64_t>(gdst)), "r"(smem_u32(smem_src)), "r"(bytes)
+               : "l"(reinterpret_cast<uint64_t>(gdst)), "r"(smem_u32(smem_src)), "r"(bytes), "l"(pol)
                : "memory");
 }
 
