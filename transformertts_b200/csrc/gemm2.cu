@@ -44,10 +44,10 @@ struct Plan {
   static_assert(!F32 || (!LN && !WS && !PAIR), "the fp32-output plan streams W, has no LayerNorm and no CTA pairs");
   static constexpr int WB = PAIR ? B_BYTES / 2 : B_BYTES;            // one W k-block as this CTA holds it
   static constexpr int W_BYTES = WS ? 4 * WB : 0;
-  static constexpr int ST = PAIR ? (WS ? (LN ? 7 : 8) : 5) : (WS ? (LN ? 3 : 4) : 3);
-  static constexpr int STAGE_BYTES = WS ? A_BYTES : A_BYTES + WB;
+  static constexpr int ST = PAIR ? (WS ? (LN ? 7 : 8) : 5) : (WS ? (LN ? 3 : 4) : (F32 ? 5 : 3));
+  static constexpr int STAGE_BYTES = WS ? A_BYTES : A_BYTES + (F32 ? WB / 2 : WB);   // F32: N <= 128, half a W block
   static constexpr int RING_OFF = W_BYTES;
-  static constexpr int NBUF_H = WS ? 2 : 3;                         // staging buffers per epilogue half
+  static constexpr int NBUF_H = (WS || F32) ? 2 : 3;                // staging buffers per epilogue half
   static constexpr int SLAB_OFF = RING_OFF + ST * STAGE_BYTES;
   static constexpr int SLAB_BYTES = F32 ? NBUF_H * (CHUNK32_BYTES + CHUNK_BYTES) : 2 * NBUF_H * CHUNK_BYTES;
   static constexpr int ID_OFF = SLAB_OFF + SLAB_BYTES;               // 64x64 bf16 identity (residual via MMA)
