@@ -154,7 +154,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "valid mel frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -502,7 +502,7 @@ def run_ours(args):
             "roofline": roofline, "kernels": kernels, "step_roofline": step_roofline,
             "ar_decode": ar, "cpu_baseline": cpu, "clocks": clocks,
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -517,9 +517,31 @@ def main():
     ap.add_argument("--no-ar", action="store_true", help="skip the AR-decode section")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline")
     args = ap.parse_args()
-    if args.impl == "reference":
-        return run_reference(args)
-    return run_ours(args)
+    # stdout carries ONE JSON line: while the run is in progress file descriptor 1 points at stderr, so banners that
+    # libraries write straight to fd 1 (NCCL's version line) cannot get in front of it
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        if args.impl == "reference":
+            return run_reference(args)
+        return run_ours(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(_STDOUT_FD, 1)
+
+
+_STDOUT_FD = None
+
+
+def emit(line):
+    """Print the result line on the real stdout."""
+    sys.stdout.flush()
+    if _STDOUT_FD is not None:
+        os.write(_STDOUT_FD, (json.dumps(line) + "\n").encode())
+    else:
+        print(json.dumps(line))
 
 
 if __name__ == "__main__":
