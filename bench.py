@@ -430,6 +430,56 @@ def run_ours(args):
                              "us_per_step": 1e3 * ms / T,
                              "achieved_gbs": (kv + wbytes) / (ms / 1e3) / 1e9}
 
+    # ---- batch-sharded AR decode (configs[3]): 512 utterances dealt in contiguous blocks to the ranks
+    # (sharding.shard_bounds), micro-batches of 32 / 64 (each one inference() call), 1000 frames each, no collective
+    ar_sharded = None
+    if not args.no_ar and not args.no_extra:
+        from transformertts_b200.sharding import shard_bounds, micro_batches
+        NU = 512
+        uph, _, upl, _ = make_batch(NU, Tp, 8, seed=300)               # the same 512 utterances on every rank
+        lo, hi = shard_bounds(NU, world, rank)
+        uph, upl = uph.to(dev), upl.to(dev)
+        ar_sharded = {"utterances": NU, "frames_each": 1000, "per_rank": hi - lo}
+        for mb in (32, 64):
+            parts = micro_batches(lo, hi, mb)
+
+            def run_block():
+                n = 0
+                for s_, e_ in parts:
+                    tp_ = int(upl[s_:e_].max())
+                    r_ = model.inference(uph[s_:e_, :tp_].contiguous(), upl[s_:e_], max_len=1001)
+                    n += (e_ - s_) * r_["pred_melspec"].shape[1]
+                return n
+            s_, e_ = parts[0]
+            model.inference(uph[s_:e_, :int(upl[s_:e_].max())].contiguous(), upl[s_:e_], max_len=1001)   # warm-up
+            barrier()
+            flush()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            nframes = run_block()
+            b.record()
+            b.synchronize()
+            ms = max_over_ranks(a.elapsed_time(b))
+            tot = sum_over_ranks(float(nframes))
+            ar_sharded[f"micro_batch_{mb}"] = {"frames_per_s": tot / (ms / 1e3), "ms_total": ms, "frames": int(tot),
+                                               "calls_per_rank": len(parts)}
+
+    # ---- long-utterance stress (configs[4]): Tp=400, Tm=2000, B=1 and B=16, alignments materialised
+    long_utt = None
+    if not args.no_extra:
+        long_utt = {}
+        for Bl in (1, 16):
+            lph, lmel, lpl, lml = (t.to(dev) for t in make_batch(Bl, 400, 2000, seed=500 + rank))
+            fn = lambda: model(lph, lmel, lpl, lml)
+            ms = max_over_ranks(time_kernel(fn, 5, flush))
+            lfl = algorithmic_flops(Bl, 400, 2000, True)
+            long_utt[f"B{Bl}"] = {"ms_per_forward": ms, "valid_frames_per_s": sum_over_ranks(float(lml.sum())) / (ms / 1e3),
+                                  "padded_frames_per_s": world * Bl * 2000 / (ms / 1e3),
+                                  "achieved_tflops": lfl / (ms / 1e3) / 1e12,
+                                  "align_bytes": 3 * Bl * H * 2000 * 400 * 4}
+            del lph, lmel, lpl, lml
+        torch.cuda.empty_cache()
+
     # ---- roofline of the dominant kernel, timed alone on this stream (burst peak)
     peaks = measured_peaks()
     roofline, kernels = None, []
@@ -500,7 +550,8 @@ def run_ours(args):
                             "reference (utils/plot.py copies single maps)"},
             "gpu_launches": launches,
             "roofline": roofline, "kernels": kernels, "step_roofline": step_roofline,
-            "ar_decode": ar, "cpu_baseline": cpu, "clocks": clocks,
+            "ar_decode": ar, "ar_sharded_512": ar_sharded, "long_utterance": long_utt,
+            "cpu_baseline": cpu, "clocks": clocks,
         }
         emit(line)
     if world > 1:
@@ -516,6 +567,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-ar", action="store_true", help="skip the AR-decode section")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline")
+    ap.add_argument("--no-extra", action="store_true",
+                    help="skip the configs[3] (512 sharded AR utterances) and configs[4] (long utterances) sections")
     args = ap.parse_args()
     # stdout carries ONE JSON line: while the run is in progress file descriptor 1 points at stderr, so banners that
     # libraries write straight to fd 1 (NCCL's version line) cannot get in front of it

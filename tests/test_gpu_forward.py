@@ -67,7 +67,8 @@ def test_forward_vs_reference_golden(golden_dir, name):
     _compare(out, ref, pl, name)
 
 
-@pytest.mark.parametrize("B,Tp,Tm,seed", [(4, 150, 800, 21), (2, 400, 1000, 22), (16, 150, 800, 23), (1, 33, 130, 24)])
+@pytest.mark.parametrize("B,Tp,Tm,seed", [(4, 150, 800, 21), (2, 400, 1000, 22), (16, 150, 800, 23), (1, 33, 130, 24),
+                                          (1, 400, 2000, 25)])   # last: BASELINE.json configs[4] at B=1
 def test_forward_vs_oracle(B, Tp, Tm, seed):
     sd = O.make_state_dict(seed)
     ph, mel, pl, ml = O.make_inputs(B, Tp, Tm, seed=seed + 1)
@@ -144,3 +145,26 @@ def test_full_size_properties_cfg2():
         assert float((A.sum(-1) - 1).abs().max()) <= 1e-3
         mask = (torch.arange(150, device=A.device)[None, :] >= pl.to(A.device)[:, None])[:, None, None, :]
         assert float((A * mask).abs().max()) == 0.0
+
+
+def test_full_size_properties_cfg5_long_utterances():
+    """BASELINE.json configs[4] (long-utterance stress: Tp=400, Tm=2000, B=16, cross-attention probabilities
+    materialised per layer / head).  Tk = 400 > 256 takes the streaming attention kernel with the probability
+    sweep, not the single-pass one of cfg 2.  B=1 is compared with the oracle in test_forward_vs_oracle; here
+    the size-independent properties: finite outputs, alignment rows sum to 1 with no mass on padded keys, and
+    the first two utterances equal a B=2 run of the same rows."""
+    sd = O.make_state_dict(51)
+    ph, mel, pl, ml = O.make_inputs(16, 400, 2000, seed=52)
+    m = _model(sd)
+    out = m(ph, mel, pl, ml)
+    sub = m(ph[:2], mel[:2], pl[:2], ml[:2])
+    torch.cuda.synchronize()
+    for k in ("pred_melspec", "post_melspec", "pred_stop"):
+        assert torch.isfinite(out[k]).all()
+        assert float((out[k][:2] - sub[k]).abs().max()) <= 1e-5, k
+    for A, S in zip(out["alignments"], sub["alignments"]):
+        assert A.shape == (16, 4, 2000, 400)
+        assert float((A.sum(-1) - 1).abs().max()) <= 1e-3
+        mask = (torch.arange(400, device=A.device)[None, :] >= pl.to(A.device)[:, None])[:, None, None, :]
+        assert float((A * mask).abs().max()) == 0.0
+        assert float((A[:2] - S).abs().max()) <= 1e-6
