@@ -428,7 +428,8 @@ def run_ours(args):
             wbytes = T * 5.75e6
             ar[f"B{Bar}"] = {"frames_per_s": world * Bar * T / (ms / 1e3), "ms_total": ms, "frames": T,
                              "us_per_step": 1e3 * ms / T,
-                             "achieved_gbs": (kv + wbytes) / (ms / 1e3) / 1e9}
+                             "achieved_gbs": (kv + wbytes) / (ms / 1e3) / 1e9,
+                             "frac_of_hbm_peak": (kv + wbytes) / (ms / 1e3) / 1e9 / measured_peaks()["hbm_gbs"]}
 
     # ---- batch-sharded AR decode (configs[3]): 512 utterances dealt in contiguous blocks to the ranks
     # (sharding.shard_bounds), micro-batches of 32 / 64 (each one inference() call), 1000 frames each, no collective
@@ -439,7 +440,7 @@ def run_ours(args):
         uph, _, upl, _ = make_batch(NU, Tp, 8, seed=300)               # the same 512 utterances on every rank
         lo, hi = shard_bounds(NU, world, rank)
         uph, upl = uph.to(dev), upl.to(dev)
-        ar_sharded = {"utterances": NU, "frames_each": 1000, "per_rank": hi - lo}
+        ar_sharded = {"utterances": NU, "frames_each": 1000, "per_rank": hi - lo, "scaling": "strong"}
         for mb in (32, 64):
             parts = micro_batches(lo, hi, mb)
 
