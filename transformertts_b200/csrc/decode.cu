@@ -36,7 +36,34 @@ struct DecSmem {
   float part[MAX_CLUSTER / 4][kH][R][PSTRIDE];   // attention partials [split][head][row]
   float wpart[DEC_WARPS][PSTRIDE]; // per-warp partials before the in-CTA combine
   int exit_flag;
+  alignas(8) uint64_t bar[3];      // data-arrival barriers of bufA / bufB / part (st.async complete_tx from all peers)
 };
+
+// Remote (DSMEM) stores that complete bytes on an mbarrier of the DESTINATION CTA: the consumer waits on its own
+// barrier for the bytes of the phase, so no release fence (MEMBAR.ALL.GPU), no cluster rendezvous and no L1
+// invalidate is paid per phase (profiles/r01_v11_decode_b1_ncu.txt: 25 % + 19 % of the step were those).
+__device__ __forceinline__ void st_async_f32(uint32_t raddr, float v, uint32_t rbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(raddr),
+               "r"(__float_as_uint(v)), "r"(rbar)
+               : "memory");
+}
+__device__ __forceinline__ void st_async_f32x4(uint32_t raddr, float a, float b, float c, float d, uint32_t rbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(raddr),
+               "r"(__float_as_uint(a)), "r"(__float_as_uint(b)), "r"(__float_as_uint(c)), "r"(__float_as_uint(d)), "r"(rbar)
+               : "memory");
+}
+
+__device__ __forceinline__ void st_async_f32x2(uint32_t raddr, float a, float b, uint32_t rbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];" ::"r"(raddr),
+               "r"(__float_as_uint(a)), "r"(__float_as_uint(b)), "r"(rbar)
+               : "memory");
+}
+template <int U>
+__device__ __forceinline__ void st_async_vec(uint32_t raddr, const float (&v)[U], uint32_t rbar) {
+  static_assert(U == 2 || U == 4, "vector width");
+  if constexpr (U == 2) st_async_f32x2(raddr, v[0], v[1], rbar);
+  else st_async_f32x4(raddr, v[0], v[1], v[2], v[3], rbar);
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -50,8 +77,8 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
 }
 
 // y[r][n] = sum_k in[r][k] * W[n][k] + bias[n] for n in [n_begin, n_end): one warp per output,
-// U outputs in flight per warp, lanes stride K in 16-byte weight loads.  emit(n, r, value) is called
-// by all 32 lanes with the reduced value.
+// U outputs in flight per warp, lanes stride K in 16-byte weight loads.  emit(n0, r, values[U]) is called
+// by all 32 lanes with the reduced values of outputs n0 .. n0+U-1 of row r.
 template <int R, int U, class Emit>
 __device__ __forceinline__ void gemv_slice(const bf16* __restrict__ W, int ldw, const float* __restrict__ bias, int K,
                                            int n_begin, int n_end, const float* in, int ld_in, Emit&& emit) {
@@ -87,14 +114,17 @@ __device__ __forceinline__ void gemv_slice(const bf16* __restrict__ W, int ldw, 
           for (int i = 0; i < 8; ++i) acc[u][r] = fmaf(wf[i], xin[r][i], acc[u][r]);
       }
     }
+    // the slices are multiples of U wide (N / C for N = 256, 768, 1024 and U = 1 for the 81 head rows), so a pass is
+    // always full: emit gets the U adjacent outputs of a row at once and can publish them as one vector store
+    float bn[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int n = nb + u;
-      if (n < n_end) {                         // warp-uniform
-        const float bn = __ldg(bias + n);
+    for (int u = 0; u < U; ++u) bn[u] = __ldg(bias + nb + u);
 #pragma unroll
-        for (int r = 0; r < R; ++r) emit(n, r, warp_sum(acc[u][r]) + bn);
-      }
+    for (int r = 0; r < R; ++r) {
+      float vals[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) vals[u] = warp_sum(acc[u][r]) + bn[u];
+      emit(nb, r, vals);
     }
   }
 }
@@ -215,7 +245,7 @@ __device__ __forceinline__ Partial attend_keys(const bf16* kv, int n_keys, const
 }
 
 template <int R>
-__global__ void __launch_bounds__(DEC_THREADS, 1) decode_kernel(const DecodeArgs a) {
+__global__ void __launch_bounds__(DEC_THREADS, R <= 2 ? 2 : 1) decode_kernel(const DecodeArgs a) {   // R <= 2: two CTAs per SM (<= 128 registers), which the one-wave plans count on
   cg::cluster_group cluster = cg::this_cluster();
   const int C = (int)cluster.num_blocks();
   const int rank = (int)cluster.block_rank();
@@ -232,8 +262,30 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_kernel(const DecodeArgs
   const int unit = split * WPR + wi, units = n_split * WPR;
 
   for (int i = tid; i < R * kMelPad; i += DEC_THREADS) (&sm.melprev[0][0])[i] = 0.f;
-  if (tid == 0) sm.exit_flag = 0;
+  if (tid == 0) {
+    sm.exit_flag = 0;
+    for (int i = 0; i < 3; ++i) mbar_init(&sm.bar[i], 1);
+    fence_mbar_init();
+  }
   cluster.sync();
+
+  // Phase protocol.  Most phases publish with st.async into every peer and wait on the local barrier of the
+  // destination buffer: thread 0 arms it with the bytes the whole cluster will deliver, everybody waits for the
+  // phase to complete.  A CTA can only reach phase p after every peer has sent phase p-1 (all its warps emit in
+  // every such phase), i.e. after every peer has finished reading what phase p overwrites.  Two phases per step keep
+  // the full cluster barrier: prenet 1 (stop flag) and the heads (K/V cache and frame visibility at GPU scope).
+  enum { BAR_A = 0, BAR_B = 1, BAR_P = 2 };
+  const uint32_t sm_base = smem_u32(&sm);
+  const uint32_t peer_base = mapa_u32(sm_base, (uint32_t)(lane % C));        // DecSmem of CTA lane % C
+  auto raddr = [&](const void* local) { return peer_base + (smem_u32(local) - sm_base); };
+  const uint32_t rbarA = raddr(&sm.bar[BAR_A]), rbarB = raddr(&sm.bar[BAR_B]);
+  uint32_t parA = 0, parB = 0, parP = 0;
+  auto arm = [&](int d, uint32_t bytes) { if (tid == 0) mbar_expect_tx(&sm.bar[d], bytes); };
+  auto arrived = [&](int d, uint32_t& parity) {
+    mbar_wait(&sm.bar[d], parity);
+    parity ^= 1u;
+    __syncthreads();
+  };
 
   auto slice = [&](int N, int& nb, int& ne) {
     const int per = (N + C - 1) / C;
@@ -245,6 +297,7 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_kernel(const DecodeArgs
 
   // ---- attention over cached keys for (arow, head); publishes the CTA's partial to every peer
   auto attention_phase = [&](const bf16* kv, int n_keys, const float* q, const float* cur_k, const float* cur_v) {
+    arm(BAR_P, (uint32_t)(C * R * 66 * 4));                      // n_split x 4 heads x R rows x (m, l, o[64])
     Partial p = attend_keys(kv, n_keys, q, head, unit, units, cur_k, cur_v);
     const int dl = lane & 7;
     if (lane < 8) {
@@ -269,17 +322,18 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_kernel(const DecodeArgs
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] += w[4 + dl * 8 + j] * c;
       }
+      const uint32_t loc = smem_u32(&sm.part[split][head][warp][0]);
       for (int p0 = 0; p0 < C; p0 += 4) {
         const int pr = p0 + (lane >> 3);
         if (pr < C) {
-          float* dst = cluster.map_shared_rank(&sm.part[split][head][warp][0], pr);
-          if (dl == 0) { dst[0] = m; dst[1] = l; }
-          *reinterpret_cast<float4*>(dst + 4 + dl * 8) = make_float4(o[0], o[1], o[2], o[3]);
-          *reinterpret_cast<float4*>(dst + 8 + dl * 8) = make_float4(o[4], o[5], o[6], o[7]);
+          const uint32_t dst = mapa_u32(loc, (uint32_t)pr), rb = mapa_u32(smem_u32(&sm.bar[BAR_P]), (uint32_t)pr);
+          if (dl == 0) { st_async_f32(dst, m, rb); st_async_f32(dst + 4, l, rb); }
+          st_async_f32x4(dst + (4 + dl * 8) * 4, o[0], o[1], o[2], o[3], rb);
+          st_async_f32x4(dst + (8 + dl * 8) * 4, o[4], o[5], o[6], o[7], rb);
         }
       }
     }
-    cluster.sync();
+    arrived(BAR_P, parP);
     // every CTA combines the key splits of all heads: thread -> (head, dim)
     {
       const int hh = tid >> 6, d = tid & 63;
@@ -326,14 +380,20 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_kernel(const DecodeArgs
     // ---- decoder prenet (model/model.py:61-67): relu(W1 mel_prev + b1)
     slice(kD, nb, ne);
     gemv_slice<R, 2>(a.w_pre1, kMelPad, a.b_pre1, kMelPad, nb, ne, &sm.melprev[0][0], kMelPad,
-                     [&](int n, int r, float v) { if (lane < C) peer->bufA[r][n] = fmaxf(v, 0.f); });
+                     [&](int n, int r, const float (&v)[2]) {
+                       if (lane < C)
+                         *reinterpret_cast<float2*>(&peer->bufA[r][n]) = make_float2(fmaxf(v[0], 0.f), fmaxf(v[1], 0.f));
+                     });
     cluster.sync();
     if (sm.exit_flag) break;
     // relu(W2 . + b2) + alpha * pe[t]   (model/model.py:95, 355-356)
-    gemv_slice<R, 2>(a.w_pre2, kD, a.b_pre2, kD, nb, ne, &sm.bufA[0][0], LDA, [&](int n, int r, float v) {
-      if (lane < C) peer->bufB[r][n] = fmaxf(v, 0.f) + a.alpha * __ldg(a.pe + (size_t)t * kD + n);
+    arm(BAR_B, R * kD * 4);
+    gemv_slice<R, 2>(a.w_pre2, kD, a.b_pre2, kD, nb, ne, &sm.bufA[0][0], LDA, [&](int n, int r, const float (&v)[2]) {
+      const float2 pe2 = __ldg(reinterpret_cast<const float2*>(a.pe + (size_t)t * kD + n));
+      if (lane < C)
+        st_async_f32x2(raddr(&sm.bufB[r][n]), fmaxf(v[0], 0.f) + a.alpha * pe2.x, fmaxf(v[1], 0.f) + a.alpha * pe2.y, rbarB);
     });
-    cluster.sync();
+    arrived(BAR_B, parB);
     for (int i = tid; i < R * kD; i += DEC_THREADS) sm.x[i / kD][i % kD] = sm.bufB[i / kD][i % kD];
     __syncthreads();
 
@@ -342,45 +402,55 @@ __global__ void __launch_bounds__(DEC_THREADS, 1) decode_kernel(const DecodeArgs
       const DecLayerW& w = a.layer[l];
       // ---- self-attention: in-proj, cache append
       slice(3 * kD, nb, ne);
-      gemv_slice<R, 4>(w.w_qkv, kD, w.b_qkv, kD, nb, ne, &sm.x[0][0], kD, [&](int n, int r, float v) {
-        if (lane < C) peer->bufA[r][n] = v;
+      arm(BAR_A, R * 3 * kD * 4);
+      gemv_slice<R, 4>(w.w_qkv, kD, w.b_qkv, kD, nb, ne, &sm.x[0][0], kD, [&](int n, int r, const float (&v)[4]) {
+        if (lane < C) st_async_vec<4>(raddr(&sm.bufA[r][n]), v, rbarA);
         if (lane == 0 && n >= kD && row_valid(r))
-          a.self_kv[(((size_t)l * a.B + row0 + r) * a.Tmax + t) * 512 + (n - kD)] = __float2bfloat16(v);
+          *reinterpret_cast<uint2*>(a.self_kv + (((size_t)l * a.B + row0 + r) * a.Tmax + t) * 512 + (n - kD)) =
+              make_uint2(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]));
       });
-      cluster.sync();
+      arrived(BAR_A, parA);
       attention_phase(a.self_kv + ((size_t)l * a.B + row_b(arow)) * a.Tmax * 512, t, &sm.bufA[arow][head * kDh],
                       &sm.bufA[arow][kD], &sm.bufA[arow][2 * kD]);
       slice(kD, nb, ne);
+      arm(BAR_B, R * kD * 4);
       gemv_slice<R, 2>(w.w_so, kD, w.b_so, kD, nb, ne, &sm.att[0][0], kD,
-                       [&](int n, int r, float v) { if (lane < C) peer->bufB[r][n] = v; });
-      cluster.sync();
+                       [&](int n, int r, const float (&v)[2]) { if (lane < C) st_async_vec<2>(raddr(&sm.bufB[r][n]), v, rbarB); });
+      arrived(BAR_B, parB);
       add_layernorm<R>(sm.x, sm.bufB, w.ln1_g, w.ln1_b);
       // ---- cross-attention over the precomputed memory K/V (keys >= phoneme_len masked)
+      arm(BAR_A, R * kD * 4);
       gemv_slice<R, 2>(w.w_cq, kD, w.b_cq, kD, nb, ne, &sm.x[0][0], kD,
-                       [&](int n, int r, float v) { if (lane < C) peer->bufA[r][n] = v; });
-      cluster.sync();
+                       [&](int n, int r, const float (&v)[2]) { if (lane < C) st_async_vec<2>(raddr(&sm.bufA[r][n]), v, rbarA); });
+      arrived(BAR_A, parA);
       attention_phase(a.cross_kv + ((size_t)l * a.B + row_b(arow)) * a.Tp * 512, min(a.ph_len[row_b(arow)], a.Tp),
                       &sm.bufA[arow][head * kDh], nullptr, nullptr);
+      arm(BAR_B, R * kD * 4);
       gemv_slice<R, 2>(w.w_co, kD, w.b_co, kD, nb, ne, &sm.att[0][0], kD,
-                       [&](int n, int r, float v) { if (lane < C) peer->bufB[r][n] = v; });
-      cluster.sync();
+                       [&](int n, int r, const float (&v)[2]) { if (lane < C) st_async_vec<2>(raddr(&sm.bufB[r][n]), v, rbarB); });
+      arrived(BAR_B, parB);
       add_layernorm<R>(sm.x, sm.bufB, w.ln2_g, w.ln2_b);
       // ---- position-wise FFN
       slice(kF, nb, ne);
-      gemv_slice<R, 4>(w.w_f1, kD, w.b_f1, kD, nb, ne, &sm.x[0][0], kD,
-                       [&](int n, int r, float v) { if (lane < C) peer->bufA[r][n] = fmaxf(v, 0.f); });
-      cluster.sync();
+      arm(BAR_A, R * kF * 4);
+      gemv_slice<R, 4>(w.w_f1, kD, w.b_f1, kD, nb, ne, &sm.x[0][0], kD, [&](int n, int r, const float (&v)[4]) {
+        if (lane < C)
+          st_async_f32x4(raddr(&sm.bufA[r][n]), fmaxf(v[0], 0.f), fmaxf(v[1], 0.f), fmaxf(v[2], 0.f), fmaxf(v[3], 0.f), rbarA);
+      });
+      arrived(BAR_A, parA);
       slice(kD, nb, ne);
+      arm(BAR_B, R * kD * 4);
       gemv_slice<R, 2>(w.w_f2, kF, w.b_f2, kF, nb, ne, &sm.bufA[0][0], LDA,
-                       [&](int n, int r, float v) { if (lane < C) peer->bufB[r][n] = v; });
-      cluster.sync();
+                       [&](int n, int r, const float (&v)[2]) { if (lane < C) st_async_vec<2>(raddr(&sm.bufB[r][n]), v, rbarB); });
+      arrived(BAR_B, parB);
       add_layernorm<R>(sm.x, sm.bufB, w.ln3_g, w.ln3_b);
     }
 
     // ---- mel + stop heads (model/model.py:376-380); the frame is fed back un-rounded
     slice(kMel + 1, nb, ne);
     int rep = 0, cnt = 0;
-    gemv_slice<R, 1>(a.w_head, kD, a.b_head, kD, nb, ne, &sm.x[0][0], kD, [&](int n, int r, float v) {
+    gemv_slice<R, 1>(a.w_head, kD, a.b_head, kD, nb, ne, &sm.x[0][0], kD, [&](int n, int r, const float (&vv)[1]) {
+      const float v = vv[0];
       if (n < kMel) {
         if (lane < C) peer->melprev[r][n] = v;
         if (lane == 0 && row_valid(r)) a.mel_out[((size_t)(row0 + r) * a.Tmax + t) * kMel + n] = v;
