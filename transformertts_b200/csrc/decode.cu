@@ -36,7 +36,7 @@ struct DecSmem {
   float part[MAX_CLUSTER / 4][kH][R][PSTRIDE];   // attention partials [split][head][row]
   float wpart[DEC_WARPS][PSTRIDE]; // per-warp partials before the in-CTA combine
   int exit_flag;
-  alignas(8) uint64_t bar[3];      // data-arrival barriers of bufA / bufB / part (st.async complete_tx from all peers)
+  alignas(8) uint64_t bar[4];      // data-arrival barriers of bufA / bufB / part / melprev (st.async complete_tx from all peers)
 };
 
 // Remote (DSMEM) stores that complete bytes on an mbarrier of the DESTINATION CTA: the consumer waits on its own
@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(DEC_THREADS, R <= 2 ? 2 : 1) decode_kernel(con
   for (int i = tid; i < R * kMelPad; i += DEC_THREADS) (&sm.melprev[0][0])[i] = 0.f;
   if (tid == 0) {
     sm.exit_flag = 0;
-    for (int i = 0; i < 3; ++i) mbar_init(&sm.bar[i], 1);
+    for (int i = 0; i < 4; ++i) mbar_init(&sm.bar[i], 1);
     fence_mbar_init();
   }
   cluster.sync();
@@ -272,14 +272,15 @@ __global__ void __launch_bounds__(DEC_THREADS, R <= 2 ? 2 : 1) decode_kernel(con
   // Phase protocol.  Most phases publish with st.async into every peer and wait on the local barrier of the
   // destination buffer: thread 0 arms it with the bytes the whole cluster will deliver, everybody waits for the
   // phase to complete.  A CTA can only reach phase p after every peer has sent phase p-1 (all its warps emit in
-  // every such phase), i.e. after every peer has finished reading what phase p overwrites.  Two phases per step keep
-  // the full cluster barrier: prenet 1 (stop flag) and the heads (K/V cache and frame visibility at GPU scope).
-  enum { BAR_A = 0, BAR_B = 1, BAR_P = 2 };
+  // every such phase), i.e. after every peer has finished reading what phase p overwrites.  One phase per step keeps
+  // the full cluster barrier: prenet 1 (stop flag; its release / acquire also makes the K/V rows that the peers
+  // appended to the cache in global memory during the previous step visible before this step's attention).
+  enum { BAR_A = 0, BAR_B = 1, BAR_P = 2, BAR_M = 3 };
   const uint32_t sm_base = smem_u32(&sm);
   const uint32_t peer_base = mapa_u32(sm_base, (uint32_t)(lane % C));        // DecSmem of CTA lane % C
   auto raddr = [&](const void* local) { return peer_base + (smem_u32(local) - sm_base); };
-  const uint32_t rbarA = raddr(&sm.bar[BAR_A]), rbarB = raddr(&sm.bar[BAR_B]);
-  uint32_t parA = 0, parB = 0, parP = 0;
+  const uint32_t rbarA = raddr(&sm.bar[BAR_A]), rbarB = raddr(&sm.bar[BAR_B]), rbarM = raddr(&sm.bar[BAR_M]);
+  uint32_t parA = 0, parB = 0, parP = 0, parM = 0;
   auto arm = [&](int d, uint32_t bytes) { if (tid == 0) mbar_expect_tx(&sm.bar[d], bytes); };
   auto arrived = [&](int d, uint32_t& parity) {
     mbar_wait(&sm.bar[d], parity);
@@ -327,7 +328,7 @@ __global__ void __launch_bounds__(DEC_THREADS, R <= 2 ? 2 : 1) decode_kernel(con
         const int pr = p0 + (lane >> 3);
         if (pr < C) {
           const uint32_t dst = mapa_u32(loc, (uint32_t)pr), rb = mapa_u32(smem_u32(&sm.bar[BAR_P]), (uint32_t)pr);
-          if (dl == 0) { st_async_f32(dst, m, rb); st_async_f32(dst + 4, l, rb); }
+          if (dl == 0) st_async_f32x2(dst, m, l, rb);
           st_async_f32x4(dst + (4 + dl * 8) * 4, o[0], o[1], o[2], o[3], rb);
           st_async_f32x4(dst + (8 + dl * 8) * 4, o[4], o[5], o[6], o[7], rb);
         }
@@ -448,11 +449,12 @@ __global__ void __launch_bounds__(DEC_THREADS, R <= 2 ? 2 : 1) decode_kernel(con
 
     // ---- mel + stop heads (model/model.py:376-380); the frame is fed back un-rounded
     slice(kMel + 1, nb, ne);
+    arm(BAR_M, R * kMel * 4);
     int rep = 0, cnt = 0;
     gemv_slice<R, 1>(a.w_head, kD, a.b_head, kD, nb, ne, &sm.x[0][0], kD, [&](int n, int r, const float (&vv)[1]) {
       const float v = vv[0];
       if (n < kMel) {
-        if (lane < C) peer->melprev[r][n] = v;
+        if (lane < C) st_async_f32(raddr(&sm.melprev[r][n]), v, rbarM);
         if (lane == 0 && row_valid(r)) a.mel_out[((size_t)(row0 + r) * a.Tmax + t) * kMel + n] = v;
       } else if (row_valid(r)) {
         if (lane == 0) a.stop_out[(size_t)(row0 + r) * a.Tmax + t] = v;
@@ -461,7 +463,7 @@ __global__ void __launch_bounds__(DEC_THREADS, R <= 2 ? 2 : 1) decode_kernel(con
       }
     });
     if (lane == 0 && rep > 0) atomicAdd(a.stop_count + t, (rep << 16) | cnt);
-    cluster.sync();
+    arrived(BAR_M, parM);        // waited in the same step: nothing is in flight towards a CTA that leaves the loop
   }
   cluster.sync();
 }
