@@ -5,10 +5,11 @@
 // times per step; here ONE kernel launch runs all steps.  A thread-block cluster owns R utterances:
 // every CTA keeps the R x 256 fp32 residual stream in shared memory, computes a 1/C slice of each
 // projection (bf16 weights streamed from L2, warp-shuffle reductions), and publishes the slice into the
-// shared memory of all C CTAs of the cluster (DSMEM), so one barrier.cluster per phase replaces a kernel
-// boundary.  Attention over the cache is split over heads x key ranges across the CTAs with 16-byte
-// coalesced K/V reads and an online softmax; partial (max, sum, o) triples are combined after the
-// barrier.  The stop rule ("all rows >= threshold at the same step", model/model.py:382-384) is evaluated
+// shared memory of all C CTAs of the cluster (DSMEM) with st.async stores that complete bytes on an mbarrier of
+// the destination CTA: a phase boundary is a local wait for the bytes of the phase (no release fence, no cluster
+// rendezvous); one barrier.cluster per step remains (stop flag, K/V cache visibility).  Attention over the
+// cache is split over heads x key ranges across the CTAs with 16-byte coalesced K/V reads and an online
+// softmax; partial (max, sum, o) triples are combined once they have arrived.  The stop rule ("all rows >= threshold at the same step", model/model.py:382-384) is evaluated
 // on the device through a per-step counter; no host round trip happens inside the loop.
 #include <cooperative_groups.h>
 
