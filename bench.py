@@ -7,11 +7,13 @@ A "step" is one teacher-forced forward (TransformerTTS.forward, model/model.py:2
 synthetic LJSpeech-shaped input; at N=1 the workload is BASELINE.json configs[1] (B=64, Tp=150, Tm=800,
 alignments returned).  With N>1 (torchrun, one rank per GPU) every rank runs the same per-GPU batch on its
 own utterances: weak scaling, no collective on the data path; the timing is the max over ranks.
-The line also carries AR-decode numbers (configs[2]), the roofline of the dominant kernel, the CPU baseline
-(the oracle port of the reference, timed on this box's host cores) and clocks sampled during the timed region.
+The line also carries AR-decode numbers (configs[2]) with their own end-to-end and CPU figures, the roofline of the
+dominant kernel, the CPU baseline and clocks sampled during the timed region.
 
-`--impl reference` times the reference's CPU implementation of the same path (the oracle port: the reference
-is pure PyTorch and /root/reference does not travel to the GPU box) with all host threads, rank 0 only.
+`--impl reference` times the reference's own CPU implementation of the same path with all host threads, rank 0 only:
+the UNMODIFIED `model.TransformerTTS` staged under oracle/_ref by oracle/make_ref.py (kind "reference"; if that
+directory did not travel, the oracle port, kind "port").  One step = one forward over BASELINE.json configs[0]
+(B=16, Tp=150, Tm=800: a 16-utterance sample of the headline batch's workload, the reference's own CPU-runnable case).
 """
 import argparse
 import json
@@ -53,7 +55,8 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed regions (device-resident steps and the
+    end-to-end runs) execute."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -64,7 +67,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -98,59 +101,118 @@ def _oracle():
     return O
 
 
-def cpu_forward_sample(B, Tp, Tm, reps, seed=1234):
-    """Times the oracle port of the reference forward on the host cores: B utterances of the cfg-2 lens law."""
-    import torch
-    O = _oracle()
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    sd = O.make_state_dict(seed)
-    ph, mel, pl, ml = O.make_inputs(B, Tp, Tm, seed=seed + 1)
-    with torch.no_grad():
-        O.forward(sd, ph, mel, pl, ml)                       # warm-up (thread pool, allocator)
-        ts = []
-        for _ in range(reps):
-            t0 = time.perf_counter()
-            O.forward(sd, ph, mel, pl, ml)
-            ts.append(time.perf_counter() - t0)
-    ts.sort()
-    med = ts[len(ts) // 2]
-    return dict(seconds=med, valid_frames=int(ml.sum()), padded_frames=B * Tm, cores=torch.get_num_threads())
+CFG1 = dict(B=16, Tp=150, Tm=800)   # BASELINE.json configs[0]: the reference's own CPU-runnable case
+
+
+class CpuReference:
+    """The reference's CPU implementation of the path: the unmodified `model.TransformerTTS` from oracle/_ref
+    (oracle/make_ref.py) when it travelled with the repo, else the oracle port.  fp32, eval, no_grad, all host threads,
+    torch's default MHA fast path left on (the stock code path)."""
+
+    def __init__(self, seed=1234):
+        import torch
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import make_ref
+        self.O = _oracle()
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        self.sd = self.O.make_state_dict(seed, stop_bias=-20.0)      # never-stop bias for the AR runs (SURVEY F10)
+        loaded = make_ref.load()
+        if loaded is not None:
+            self.kind = "reference"
+            self.module = loaded[0](**self.O.CONFIG, device="cpu").eval()
+            self.module.load_state_dict(self.sd, strict=True)
+        else:
+            self.kind, self.module = "port", None
+        self.threads = torch.get_num_threads()
+
+    def forward(self, ph, mel, pl, ml):
+        import torch
+        with torch.no_grad():
+            if self.module is not None:
+                return self.module(ph, mel, pl, ml)
+            return self.O.forward(self.sd, ph, mel, pl, ml)
+
+    def inference(self, ph, pl, max_len):
+        """model/model.py:323-394 as-is: no KV cache, the whole prefix recomputed every step."""
+        import torch
+        with torch.no_grad():
+            if self.module is not None:
+                return self.module.inference(ph, pl, max_len=max_len)
+            return self.O.inference(self.sd, ph, pl, max_len=max_len)
+
+    def describe(self):
+        return ("unmodified reference model.TransformerTTS (oracle/_ref), fp32, eval, no_grad" if self.kind == "reference"
+                else "oracle port of the reference (oracle/_ref absent), fp32 torch")
+
+
+def cpu_baselines(reps=3, ar_frames=200):
+    """Bounded CPU sample for the `cpu_baseline` objects (rank 0, N=1): configs[0] forward + the AR loop at B=1 / B=32
+    for `ar_frames` of the 1000 frames (the reference recomputes the prefix: O(T^2), so the full horizon takes minutes)."""
+    ref = CpuReference()
+    ph, mel, pl, ml = make_batch(CFG1["B"], CFG1["Tp"], CFG1["Tm"], seed=1)
+    ref.forward(ph, mel, pl, ml)                              # warm-up (thread pool, allocator)
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        ref.forward(ph, mel, pl, ml)
+        ts.append(time.perf_counter() - t0)
+    sec = sorted(ts)[len(ts) // 2]
+    fwd = {"value": int(ml.sum()) / sec, "unit": "valid mel frames/s", "cores": ref.threads, "kind": ref.kind,
+           "sample": f"configs[0] exactly: B=16, Tp=150, Tm=800 (16 utterances of the headline batch's lens law), median of "
+                     f"{reps} after 1 warm-up, {sec:.3f} s per forward; {ref.describe()}"}
+    ar = {}
+    for Bar in (1, 32):
+        aph, _, apl, _ = make_batch(Bar, CFG1["Tp"], 8, seed=100)
+        t0 = time.perf_counter()
+        r = ref.inference(aph, apl, max_len=ar_frames + 1)
+        sec = time.perf_counter() - t0
+        T = r["pred_melspec"].shape[1]
+        ar[f"B{Bar}"] = {"value": Bar * T / sec, "unit": "mel frames/s", "cores": ref.threads, "kind": ref.kind,
+                         "sample": f"reference inference() as-is (no KV cache), B={Bar}, Tp=150, first {T} of the 1000 "
+                                   f"frames, one run, {sec:.2f} s; throughput falls further with length (O(T^2))"}
+    return fwd, ar
+
+
+def our_config(world):
+    """`config` of the JSON line; the reference arm prints the same object (same workload, metric and unit)."""
+    c = {"workload": "configs[1]: teacher-forced forward, B=64 per GPU, Tp=150, Tm=800, alignments "
+                     "returned (3x[B,4,Tm,Tp] fp32)",
+         "batch_per_gpu": CFG2["B"], "parallelism": f"batch-sharded x{world}, no collective",
+         "l2": "256 MiB buffer written between timed iterations; working set (475 MB) also exceeds L2",
+         "weights": "random init (reference init laws), bf16 on the GPU arm / fp32 on the CPU arm"}
+    return c
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU path (oracle port, all host threads), same metric/config."""
+    """--impl reference: the reference's own CPU implementation, same metric / unit / config; one step = one forward over
+    a bounded sample of the workload (configs[0]: 16 utterances of the same lens law)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    B = 8                                                    # bounded sample of the cfg-2 batch (same lens law)
-    times, frames = [], 0
-    import torch
-    O = _oracle()
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    sd = O.make_state_dict(1234)
-    ph, mel, pl, ml = O.make_inputs(B, CFG2["Tp"], CFG2["Tm"], seed=1235)
+    ref = CpuReference()
+    ph, mel, pl, ml = make_batch(CFG1["B"], CFG1["Tp"], CFG1["Tm"], seed=1)
     frames = int(ml.sum())
-    with torch.no_grad():
-        for _ in range(args.warmup):
-            O.forward(sd, ph, mel, pl, ml)
-        for _ in range(args.steps):
-            t0 = time.perf_counter()
-            O.forward(sd, ph, mel, pl, ml)
-            times.append(time.perf_counter() - t0)
+    times = []
+    for _ in range(max(args.warmup, 1)):
+        ref.forward(ph, mel, pl, ml)
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        ref.forward(ph, mel, pl, ml)
+        times.append(time.perf_counter() - t0)
     ms = 1e3 * sum(times) / len(times)
     value = frames / (ms / 1e3)
-    sample = f"{B} of the 64 utterances of configs[1] per step (same lens law), oracle port of the reference, fp32"
+    sample = (f"each step: configs[0] exactly (B=16, Tp=150, Tm=800; {frames} valid frames), i.e. 16 utterances of the "
+              f"64-utterance workload; {ref.describe()}, torch.set_num_threads({ref.threads})")
     line = {
         "impl": "reference", "metric": "mel frames/sec (teacher-forced forward)", "value": value,
         "unit": "valid mel frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": "configs[1]: teacher-forced forward, Tp=150, Tm=800, alignments returned",
-                   "sample_batch": B, "valid_frames_per_step": frames, "padded_frames_per_step": B * CFG2["Tm"]},
-        "cpu_baseline": {"value": value, "unit": "valid mel frames/s", "cores": torch.get_num_threads(),
-                         "kind": "port", "sample": sample},
+        "config": our_config(1),
+        "frames": {"batch": CFG1["B"], "valid_frames_per_step": frames, "padded_frames_per_step": CFG1["B"] * CFG1["Tm"]},
+        "cpu_baseline": {"value": value, "unit": "valid mel frames/s", "cores": ref.threads, "kind": ref.kind,
+                         "sample": sample},
         "e2e": {"value": value, "unit": "valid mel frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -241,8 +303,41 @@ def dominant_kernel_candidates(model, B, Tp, Tm, dev):
                                         C.c_void_p(ckv.data_ptr() + 2 * D), 2 * D, B, Tm, Tp, _ext.ptr(plen), 0,
                                         _ext.ptr(co), _ext.ptr(probs), st()), "tts_op_attention")
 
-    keep = (A, W, W2, bias, b2, g, be, out, qkv, o, klen, cq, ckv, co, probs, plen)
+    # the persistent GEMM family, one shape per plan (profiles/README.md: 48 % of the step in round 1)
+    Wq = (torch.randn(3 * D, D, device=dev) / 16).to(torch.bfloat16)
+    bq = torch.zeros(3 * D, device=dev)
+    oq = torch.empty(Nm, 3 * D, dtype=torch.bfloat16, device=dev)
+
+    def qkv_proj():    # W-stationary plan: decoder self-attention in-projection
+        _ext.check(lib.tts_op_linear(_ext.ptr(A), _ext.ptr(Wq), _ext.ptr(bq), Nm, 3 * D, D, 0, None, 0.0, 0, None, None,
+                                     None, _ext.ptr(oq), None, st()), "tts_op_linear")
+
+    Wo = (torch.randn(D, D, device=dev) / 16).to(torch.bfloat16)
+    res = torch.randn(Nm, D, device=dev).to(torch.bfloat16)
+
+    def out_ln():      # W-stationary + residual + LayerNorm on CTA pairs: attention out-projection
+        _ext.check(lib.tts_op_linear(_ext.ptr(A), _ext.ptr(Wo), _ext.ptr(b2), Nm, D, D, 0, None, 0.0, 0, _ext.ptr(res),
+                                     _ext.ptr(g), _ext.ptr(be), _ext.ptr(out), None, st()), "tts_op_linear")
+
+    Wc = (torch.randn(D, KS * D, device=dev) / 36).to(torch.bfloat16)
+    xc = torch.randn(B, Tm, D, device=dev).to(torch.bfloat16)
+    oc = torch.empty(B, Tm, D, dtype=torch.bfloat16, device=dev)
+
+    def conv():        # streamed-W plan on CTA pairs: PostNet Conv1d 256 -> 256, k = 5, folded BN, tanh
+        _ext.check(lib.tts_op_conv1d(_ext.ptr(xc), _ext.ptr(Wc), _ext.ptr(b2), B, Tm, D, D, KS, 2, None, _ext.ptr(oc), None,
+                                     st()), "tts_op_conv1d")
+
+    keep = (A, W, W2, bias, b2, g, be, out, qkv, o, klen, cq, ckv, co, probs, plen, Wq, bq, oq, Wo, res, Wc, xc, oc)
     return [
+        dict(key="gemm2_qkv", name="gemm2_kernel W-stationary: decoder QKV projection (51200 x 768 x 256, bias)",
+             bound="tensor", work=2.0 * Nm * 3 * D * D, per_step=3, fn=qkv_proj, keep=keep,
+             hbm_bytes=float(Nm * D * 2 + Nm * 3 * D * 2)),
+        dict(key="gemm2_out_ln", name="gemm2_kernel W-stationary + LN on CTA pairs: attention out-projection + residual + "
+             "LayerNorm (51200 x 256 x 256)", bound="tensor", work=2.0 * Nm * D * D, per_step=6, fn=out_ln, keep=keep,
+             hbm_bytes=float(3 * Nm * D * 2)),
+        dict(key="gemm2_conv", name="gemm2_kernel streamed W on CTA pairs: PostNet Conv1d 256 -> 256 k5 + BN + tanh "
+             "(51200 x 256 x 1280)", bound="tensor", work=2.0 * Nm * D * D * KS, per_step=3, fn=conv, keep=keep,
+             hbm_bytes=float(2 * Nm * D * 2)),
         dict(key="ffn_fused", name="ffn_kernel decoder FFN block (51200 rows, 256 -> 1024 -> 256, bias+ReLU, residual, "
              "LayerNorm; CTA pairs, hidden activation in tensor memory)", bound="tensor",
              work=4.0 * Nm * F * D, per_step=3, fn=gemm, keep=keep),
@@ -274,6 +369,15 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # one process per GPU on a shared host: give every rank its own slice of the cores, so the feeder / fetcher
+        # threads of the ranks do not migrate over each other (the e2e path is host-side bound at N = 8)
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            per = len(cores) // world
+            if per >= 1:
+                os.sched_setaffinity(0, cores[local * per:(local + 1) * per])
+        except (AttributeError, OSError):
+            pass
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # rank 0 prints ONE JSON line on stdout: NCCL's banner / debug lines go to stderr whatever NCCL_DEBUG says
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
@@ -338,76 +442,83 @@ def run_ours(args):
     total_padded = padded * world
     value = total_valid / (ms_step / 1e3)
 
-    # ---- end to end through the public API with host buffers (pinned H2D in, D2H of the mel/stop result out)
-    hout = {k: torch.empty_like(out[k], device="cpu").pin_memory() for k in ("pred_melspec", "post_melspec", "pred_stop")}
-    h2d = sum(t.numel() * t.element_size() for t in (hph, hmel, hpl, hml))
-    d2h = sum(t.numel() * t.element_size() for t in hout.values())
+    # ---- end to end through the public API with host buffers: the package's own feeder / fetcher (transformertts_b200.data:
+    # SURVEY 8(f) rank 3).  Every step: collated pinned host batch -> device on a copy stream, forward through the module,
+    # pred | post | stop -> pinned host with ONE copy on a third stream; double-buffered, so the copies of neighbouring
+    # steps overlap the forward.  Timed by wall clock around K steps incl. the final drain; median of 3 runs.
+    from transformertts_b200 import TransformerTTSLoss
+    from transformertts_b200.data import OutputFetcher, PinnedFeeder
+    host_f32 = {"phoneme": hph, "melspec": hmel, "phoneme_lens": hpl, "melspec_lens": hml}
+    host_b16 = dict(host_f32, melspec=hmel.to(torch.bfloat16).pin_memory())   # what data.collate_fn(mel_dtype=bf16) yields
+    crit = TransformerTTSLoss(stop_weight=8.0).to(dev)
+    loss_host = torch.empty(4).pin_memory()
 
-    # Double-buffered pipeline, the way a data loader feeds the module: step i+1's inputs travel host -> device on a
-    # copy stream while step i computes, and step i's results travel device -> host on a third stream while step
-    # i+1 computes.  Every step's inputs come from pinned host memory and every step's results land in pinned host
-    # memory inside the timed region; the last results are checked against the device-resident run.
-    NBUF = 2
-    s_in, s_out, s_main = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.current_stream(dev)
-    din = [[torch.empty_like(t, device=dev) for t in (hph, hmel, hpl, hml)] for _ in range(NBUF)]
-    houts = [{k: torch.empty_like(v) for k, v in hout.items()} for _ in range(NBUF)]
-    houts = [{k: v.pin_memory() for k, v in d.items()} for d in houts]
+    def e2e_variant(host_batch, out_dtype=torch.float32, with_align=False, loss_only=False, compute=True, check=False):
+        fetch = None if loss_only else OutputFetcher(dev, dtype=out_dtype, with_alignments=with_align)
+        static = {"o": None}
+        bytes_io = [0, 0]
 
-    def e2e_run(n):
-        ev_in, ev_done, ev_out, keep = [None] * NBUF, [None] * NBUF, [None] * NBUF, [None] * NBUF
+        def run(n):
+            feeder = PinnedFeeder((host_batch for _ in range(n)), dev)
+            last = None
+            for b in feeder:
+                if compute or static["o"] is None:
+                    o = model(b["phoneme"], b["melspec"], b["phoneme_lens"], b["melspec_lens"])
+                    static["o"] = o
+                else:
+                    o = static["o"]                       # copy-only probe: the same device buffers travel every step
+                if loss_only:
+                    l = crit(o, b["melspec"], b["melspec_lens"])
+                    loss_host.copy_(torch.stack([l["total"], l["pred_mel"], l["post_mel"], l["stop"]]), non_blocking=True)
+                    bytes_io[1] = 16
+                else:
+                    last = fetch(o)
+                    bytes_io[1] = fetch.d2h_bytes
+                bytes_io[0] = feeder.h2d_bytes
+            if fetch is not None:
+                fetch.wait()
+            torch.cuda.synchronize()
+            return last
 
-        def feed(i):
-            sl = i % NBUF
-            with torch.cuda.stream(s_in):
-                if ev_done[sl] is not None:
-                    s_in.wait_event(ev_done[sl])          # the forward that read this input buffer has finished
-                for d, h in zip(din[sl], (hph, hmel, hpl, hml)):
-                    d.copy_(h, non_blocking=True)
-                ev_in[sl] = torch.cuda.Event()
-                ev_in[sl].record(s_in)
-
-        feed(0)
-        for i in range(n):
-            sl = i % NBUF
-            if i + 1 < n:
-                feed(i + 1)
-            s_main.wait_event(ev_in[sl])
-            o = model(*din[sl])
-            ev_done[sl] = torch.cuda.Event()
-            ev_done[sl].record(s_main)
-            if ev_out[sl] is not None:
-                ev_out[sl].synchronize()                  # host buffer of step i-NBUF has been read back
-            with torch.cuda.stream(s_out):
-                s_out.wait_event(ev_done[sl])
-                for k, t in houts[sl].items():
-                    o[k].record_stream(s_out)
-                    t.copy_(o[k], non_blocking=True)
-                ev_out[sl] = torch.cuda.Event()
-                ev_out[sl].record(s_out)
-            keep[sl] = o
-        torch.cuda.synchronize()
-        return houts[(n - 1) % NBUF]
-
-    last = e2e_run(3)
-    e2e_runs = []
-    for _ in range(3):                                    # wall-clock timing of host + copies + device: median of 3 x K steps
+        run(3)
+        runs = []
+        for _ in range(3):
+            barrier()
+            t0 = time.perf_counter()
+            last = run(args.steps)
+            runs.append((time.perf_counter() - t0) / args.steps)
         barrier()
-        t0 = time.perf_counter()
-        last = e2e_run(args.steps)
-        e2e_runs.append((time.perf_counter() - t0) / args.steps)
-    barrier()
-    e2e_s = sorted(e2e_runs)[1]
-    for k in hout:
-        assert torch.equal(last[k], out[k].cpu()), f"e2e result {k} differs from the device-resident run"
-    e2e_s = max_over_ranks(e2e_s)
+        if check:                                         # the fetched host tensors equal the device-resident run
+            for k in ("pred_melspec", "post_melspec", "pred_stop"):
+                assert torch.equal(last[k], out[k].cpu()), f"e2e result {k} differs from the device-resident run"
+        sec = max_over_ranks(sorted(runs)[1])
+        return {"value": total_valid / sec, "ms_per_step": sec * 1e3, "h2d_bytes_per_step": bytes_io[0],
+                "d2h_bytes_per_step": bytes_io[1], "runs_ms_per_step": [x * 1e3 for x in runs]}
+
+    e2e_main = e2e_variant(host_b16, check=True)
+    e2e_variants = {}
+    if not args.no_extra:
+        e2e_variants = {
+            "f32_mel_in_f32_out": e2e_variant(host_f32, check=True),
+            "bf16_mel_in_bf16_packed_out": e2e_variant(host_b16, out_dtype=torch.bfloat16),
+            "validation_step_loss_only": e2e_variant(host_f32, loss_only=True),
+            "with_alignments_d2h": e2e_variant(host_b16, with_align=True),
+            "copy_only_probe": e2e_variant(host_b16, compute=False),
+        }
     clocks = sampler.stop() if rank == 0 else None
-    e2e_value = total_valid / e2e_s
+
+    # ---- configs[0] (B=16, Tp=150, Tm=800) on the GPU: the same-config counterpart of the CPU arm's step
+    c1 = [t.to(dev) for t in make_batch(CFG1["B"], CFG1["Tp"], CFG1["Tm"], seed=1)]
+    ms1 = max_over_ranks(time_kernel(lambda: model(*c1), 10, flush))
+    cfg1 = {"workload": "configs[0]: B=16, Tp=150, Tm=800, alignments returned (the CPU arm's step, same batch)",
+            "ms_per_forward": ms1, "valid_frames_per_s": world * float(c1[3].sum()) / (ms1 / 1e3)}
 
     # ---- AR decode (configs[2]): B=1 and B=32, Tp=150, 1000 frames, never-stop bias; whole inference() call
     ar = {}
     if not args.no_ar:
         for Bar in (1, 32):
             aph, _, apl, _ = make_batch(Bar, Tp, 8, seed=100 + rank)
+            haph, hapl = aph.pin_memory(), apl.pin_memory()
             aph, apl = aph.to(dev), apl.to(dev)
             model.inference(aph, apl, max_len=1001)
             torch.cuda.synchronize()
@@ -423,13 +534,30 @@ def run_ours(args):
             ts.sort()
             T = r["pred_melspec"].shape[1]
             ms = max_over_ranks(ts[1])
+            # end to end: host phonemes in (pinned), mel_pre / mel_post / stop back in pinned host memory, wall clock
+            hres = {k: torch.empty_like(v, device="cpu").pin_memory() for k, v in r.items()}
+            es = []
+            for _ in range(3):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                r2 = model.inference(haph, hapl, max_len=1001)
+                for k, v in r2.items():
+                    hres[k].copy_(v, non_blocking=True)
+                torch.cuda.synchronize()
+                es.append(time.perf_counter() - t0)
+            e_s = max_over_ranks(sorted(es)[1])
             # algorithmic bytes: self-KV reads sum_t B*L*2*t*d*2 + cross-KV reads + weights once per step
             kv = Bar * L * 2 * D * 2 * (T * (T - 1) / 2) + T * Bar * L * 2 * Tp * D * 2
             wbytes = T * 5.75e6
             ar[f"B{Bar}"] = {"frames_per_s": world * Bar * T / (ms / 1e3), "ms_total": ms, "frames": T,
                              "us_per_step": 1e3 * ms / T,
                              "achieved_gbs": (kv + wbytes) / (ms / 1e3) / 1e9,
-                             "frac_of_hbm_peak": (kv + wbytes) / (ms / 1e3) / 1e9 / measured_peaks()["hbm_gbs"]}
+                             "frac_of_hbm_peak": (kv + wbytes) / (ms / 1e3) / 1e9 / measured_peaks()["hbm_gbs"],
+                             "e2e": {"value": world * Bar * T / e_s, "unit": "mel frames/s", "ms_total": e_s * 1e3,
+                                     "h2d_bytes_per_step": int(haph.numel() * 8 + hapl.numel() * 8),
+                                     "d2h_bytes_per_step": int(sum(v.numel() * 4 for v in hres.values())),
+                                     "note": "one step = one inference() call: pinned host phonemes in, encoder + 1000 "
+                                             "decode steps + PostNet, pred / post / stop copied to pinned host memory"}}
 
     # ---- batch-sharded AR decode (configs[3]): 512 utterances dealt in contiguous blocks to the ranks
     # (sharding.shard_bounds), micro-batches of 32 / 64 (each one inference() call), 1000 frames each, no collective
@@ -489,6 +617,8 @@ def run_ours(args):
             ms = time_kernel(c["fn"], 10, flush)
             k = {"name": c["name"], "bound": c["bound"], "ms_per_launch": ms, "launches_per_step": c["per_step"],
                  "share_of_step": c["per_step"] * ms / ms_step, "traffic": ncu_traffic(c["key"])}
+            if "hbm_bytes" in c:      # the K = 256 GEMMs are memory bound by construction: show that roofline too
+                k["hbm_frac"] = c["hbm_bytes"] / (ms / 1e3) / 1e9 / peaks["hbm_gbs"]
             if c["bound"] == "tensor":
                 k.update(achieved=c["work"] / (ms / 1e3) / 1e12, peak=peaks["tf_burst"], unit="TFLOP/s")
             else:
@@ -525,30 +655,28 @@ def run_ours(args):
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only): bounded sample of the same workload
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        s = cpu_forward_sample(8, Tp, Tm, reps=3)
-        cpu = {"value": s["valid_frames"] / s["seconds"], "unit": "valid mel frames/s", "cores": s["cores"],
-               "kind": "port",
-               "sample": f"8 of the 64 utterances of configs[1] (same lens law), median of 3 after 1 warm-up, "
-                         f"{s['seconds']:.2f} s per forward, oracle port of the reference in fp32 torch"}
+        cpu, cpu_ar = cpu_baselines(reps=3, ar_frames=200)
+        for k, v in cpu_ar.items():
+            if k in ar:
+                ar[k]["cpu_baseline"] = v
 
     if rank == 0:
         line = {
             "metric": "mel frames/sec (teacher-forced forward)", "value": value, "unit": "valid mel frames/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "configs[1]: teacher-forced forward, B=64 per GPU, Tp=150, Tm=800, alignments "
-                                   "returned (3x[B,4,Tm,Tp] fp32)",
-                       "batch_per_gpu": B, "valid_frames_per_step": total_valid, "padded_frames_per_step": total_padded,
-                       "padded_frames_per_s": total_padded / (ms_step / 1e3), "parallelism": f"batch-sharded x{world}, no collective",
-                       "l2": "256 MiB buffer written between timed iterations; working set (475 MB) also exceeds L2",
-                       "weights": "random init (reference init laws), bf16"},
-            "e2e": {"value": e2e_value, "unit": "valid mel frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_s * 1e3,
-                    "runs_ms_per_step": [x * 1e3 for x in e2e_runs],
-                    "note": "median of 3 runs of K steps; every step: pinned host inputs -> device (copy stream), forward through the public module "
-                            "API, pred/post/stop -> pinned host (copy stream); double-buffered so copies of "
-                            "neighbouring steps overlap the forward; alignments stay on the device as in the "
-                            "reference (utils/plot.py copies single maps)"},
+            "config": our_config(world),
+            "frames": {"valid_frames_per_step": total_valid, "padded_frames_per_step": total_padded,
+                       "padded_frames_per_s": total_padded / (ms_step / 1e3)},
+            "e2e": dict(e2e_main, unit="valid mel frames/s",
+                        note="median of 3 runs of K steps through transformertts_b200.data.PinnedFeeder / OutputFetcher: every "
+                             "step a collated pinned host batch (bf16 target mel, as data.collate_fn(mel_dtype=bfloat16) "
+                             "yields; the kernels round the mel to bf16 either way and the result is bit-identical) -> device "
+                             "on a copy stream, forward through the public module API, pred | post | stop (fp32, one "
+                             "allocation) -> pinned host with one copy on a third stream; double-buffered; the fetched "
+                             "tensors are checked bit-equal against the device-resident run; alignments stay on the device "
+                             "as in the reference (utils/plot.py copies single maps); see e2e_variants for the other mixes"),
+            "e2e_variants": e2e_variants, "cfg1_b16": cfg1,
             "gpu_launches": launches,
             "roofline": roofline, "kernels": kernels, "step_roofline": step_roofline,
             "ar_decode": ar, "ar_sharded_512": ar_sharded, "long_utterance": long_utt,

@@ -13,6 +13,9 @@
  *   tts_encode           encoder half of TransformerTTS.inference   model/model.py:342-348
  *   tts_decode           AR loop of TransformerTTS.inference    model/model.py:351-384
  *   tts_postnet          PostNet + residual                     model/model.py:129-135, 310, 388
+ *   tts_teacher_forcing_mix   block_mask + apply_teacher_forcing  utils/util.py:103-120
+ *   tts_loss             TransformerTTSLoss.forward              loss.py:15-55
+ *   tts_pack_outputs     (no reference counterpart) pred/post/stop -> one bf16 buffer for a single D2H copy
  *   tts_op_linear / tts_op_conv1d / tts_op_attention / tts_op_ffn
  *                        the torch.nn operators underneath (model/module.py:4-53,
  *                        torch/nn/functional.py:5798,6620-6665), exported for per-operator parity tests
@@ -27,12 +30,14 @@
 extern "C" {
 #endif
 
-#define TTS_ABI_VERSION 2
+#define TTS_ABI_VERSION 3
 
 /* flags */
 #define TTS_FLAG_WANT_ALIGN 1 /* tts_forward: store cross-attention probabilities into `align` */
 #define TTS_FLAG_SERIAL 4     /* tts_forward: run the encoder branch on the caller's stream instead of the side stream */
 #define TTS_FLAG_ENC_MASK 2   /* apply the phoneme key-padding mask in the encoder (forward: yes, inference: no) */
+#define TTS_FLAG_MEL_BF16 8   /* tts_forward: `mel` is bf16 [B][Tm][80] (16-byte aligned) instead of f32: halves the
+                                 host -> device bytes of a step and skips the cast kernel (SURVEY 8(b) mel_bf16_or_f32) */
 
 /* activation codes for the operator-level entry points */
 #define TTS_ACT_NONE 0
@@ -83,10 +88,12 @@ uint64_t tts_launch_count(void);
 /* Bytes of scratch the calls below need for these sizes (Tm = frames; for tts_decode pass max frames). */
 size_t tts_workspace_bytes(int B, int Tp, int Tm);
 
-/* Teacher-forced forward.  phoneme i64 [B][Tp], mel f32 [B][Tm][80], lens i64 [B] (1 <= len <= T).
+/* Teacher-forced forward.  phoneme i64 [B][Tp], mel f32 [B][Tm][80] (bf16 with TTS_FLAG_MEL_BF16), lens i64 [B]
+ * (1 <= len <= T).  Not re-entrant per device unless TTS_FLAG_SERIAL is set: the encoder branch uses one side stream
+ * and one fork/join event pair per device, so concurrent callers on one device must serialise or pass TTS_FLAG_SERIAL.
  * Outputs f32: mel_pre [B][Tm][80], mel_post [B][Tm][80], stop [B][Tm], align [3][B][4][Tm][Tp]
  * (align may be NULL unless TTS_FLAG_WANT_ALIGN). */
-int tts_forward(const TtsWeights* w, const int64_t* phoneme, const float* mel, const int64_t* ph_lens,
+int tts_forward(const TtsWeights* w, const int64_t* phoneme, const void* mel, const int64_t* ph_lens,
                 const int64_t* mel_lens, int B, int Tp, int Tm, int flags, float* mel_pre, float* mel_post,
                 float* stop, float* align, void* workspace, size_t ws_bytes, void* stream);
 
@@ -111,6 +118,30 @@ int tts_decode_max_clusters(int rows_per_cluster, int cluster_size);
 /* PostNet with residual: mel_post = PostNet(mel_pre) + mel_pre, f32 [B][T][80] both. */
 int tts_postnet(const TtsWeights* w, const float* mel_pre, int B, int T, float* mel_post, void* workspace,
                 size_t ws_bytes, void* stream);
+
+/* ---- forward-only pieces of the training / validation step ---- */
+
+/* Block-wise scheduled sampling (utils/util.py:103-120).  seed u8 [B][T]: 1 where the reference's
+ * `torch.rand(B,1,T) < 1 - p_tf` is true (the caller draws it, so parity tests are deterministic).  The seed is dilated
+ * like max_pool1d(kernel L_bar, stride 1, padding L_bar/2)[:T]; out = where(mask, pred, mel) * (t < mel_lens[b]).
+ * pred, mel, out f32 [B][T][80]; out may alias neither input. */
+int tts_teacher_forcing_mix(const float* pred, const float* mel, const uint8_t* seed, const int64_t* mel_lens, int B,
+                            int T, int L_bar, float* out, void* stream);
+
+/* Bytes of scratch tts_loss needs on the current device (per-block partial sums). */
+size_t tts_loss_scratch_bytes(void);
+
+/* TransformerTTSLoss.forward (loss.py:15-55) over the valid frames t < mel_lens[b]:
+ * out4 f32 [4] (device) = { total, pred_mel, post_mel, stop } with pred_mel = MSE(pred, mel), post_mel = MSE(post, mel),
+ * stop = BCE-with-logits(stop, [t == len-1], pos_weight), total = pred_mel + 0.5 post_mel + stop.
+ * pred/post/mel f32 [B][T][80], stop f32 [B][T].  Deterministic (fixed reduction order). */
+int tts_loss(const float* pred, const float* post, const float* stop, const float* mel, const int64_t* mel_lens, int B,
+             int T, float pos_weight, float* out4, void* scratch, size_t scratch_bytes, void* stream);
+
+/* pred / post f32 [rows][80] + stop f32 [rows] -> packed bf16 [rows][168] (cols 0-79 pred, 80-159 post, 160 stop,
+ * 161-167 zero): one buffer, one device -> host copy per step at half the bytes. */
+int tts_pack_outputs(const float* pred, const float* post, const float* stop, long long rows, void* packed_bf16,
+                     void* stream);
 
 /* ---- operator-level entry points (used by the parity tests; same kernels as above) ---- */
 

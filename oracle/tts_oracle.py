@@ -425,6 +425,13 @@ def plant_stop_bias(sd, phoneme: Tensor, phoneme_lens: Tensor, horizon: int, min
     sd2 = dict(sd)
     sd2["linear2.linear.bias"] = torch.tensor([-1.0e4])
     z = inference_cached(sd2, phoneme, phoneme_lens, max_len=horizon + 1)["pred_stop"][..., 0] + 1.0e4
+    return plant_from_logits(z, min_t=min_t, delta=delta)
+
+
+def plant_from_logits(z: Tensor, min_t: int = 8, delta: float = 0.25):
+    """The chooser half of :func:`plant_stop_bias`: z (B,T) are the bias-free stop logits of a never-stopping run.
+    Picks the step >= min_t at which the all-rows minimum makes its largest new maximum (gap >= 2 delta) and returns
+    (bias_value, n_frames, margin) so that step is the first one where every row crosses."""
     m = z.min(dim=0).values                      # (T,) the all-rows rule looks at the min
     best = None
     run_max = float(m[0])

@@ -67,13 +67,14 @@ def op_linear(A, W, bias, act=0, pe=None, alpha=0.0, pe_period=0, residual=None,
     rd = dev_bf16(residual) if residual is not None else None
     g = dev_f32(ln[0]) if ln is not None else None
     b = dev_f32(ln[1]) if ln is not None else None
-    o16 = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+    # one kernel family, two output plans: fp32 (+ optional bf16 copy) for N <= 128, bf16 only for N % 256 == 0
+    o16 = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=DEV) if (not want_f32 or N % 8 == 0) else None
     o32 = torch.full((M, N), float("nan"), dtype=torch.float32, device=DEV) if want_f32 else None
     _ext.check(lib.tts_op_linear(_ext.ptr(Ad), _ext.ptr(Wd), _ext.ptr(bd), M, N, Kp, act, _ext.ptr(ped), float(alpha),
                                  int(pe_period), _ext.ptr(rd), _ext.ptr(g), _ext.ptr(b), _ext.ptr(o16), _ext.ptr(o32),
                                  stream()), "tts_op_linear")
     torch.cuda.synchronize()
-    return o16.float().cpu(), (o32.cpu() if want_f32 else None)
+    return (o16.float().cpu() if o16 is not None else None), (o32.cpu() if want_f32 else None)
 
 
 def ref_linear(A, W, bias, act=0, pe=None, alpha=0.0, pe_period=0, residual=None, ln=None):

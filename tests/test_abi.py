@@ -32,7 +32,7 @@ def test_ctypes_table_matches_header():
 
 def test_abi_version_and_workspace_size():
     lib = _ext.load()
-    assert lib.tts_abi_version() == 2
+    assert lib.tts_abi_version() == 3
     assert lib.tts_workspace_bytes(0, 10, 10) == 0
     a, b = lib.tts_workspace_bytes(4, 150, 800), lib.tts_workspace_bytes(8, 150, 800)
     assert 0 < a < b and a % 1024 == 0

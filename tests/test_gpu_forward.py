@@ -126,6 +126,45 @@ def test_forward_rejects_training_mode_and_bad_config():
         TransformerTTS(d_model=512, device=DEV)
 
 
+def _oracle_rows(sd, ph, mel, pl, ml, rows):
+    """Utterances are independent in eval mode, so the oracle run on a SUBSET of the rows of a batch, at
+    the same padded Tp / Tm, is an exact oracle for those rows.  The subset must contain a full-length phoneme row (row
+    0 after the sort) and a full-length mel row so that the oracle's masks keep the batch's padded widths."""
+    rows = sorted(set(rows) | {0, int(torch.argmax(ml))})
+    assert int(pl[rows].max()) == ph.shape[1] and int(ml[rows].max()) == mel.shape[1]
+    idx = torch.tensor(rows)
+    return rows, O.forward(sd, ph[idx], mel[idx], pl[idx], ml[idx])
+
+
+def _take(out, rows):
+    idx = torch.tensor(rows)
+    sub = {k: out[k].cpu()[idx] for k in ("pred_melspec", "post_melspec", "pred_stop")}
+    sub["alignments"] = [a.cpu()[idx] for a in out["alignments"]]
+    return sub
+
+
+def test_cfg2_rows_vs_oracle():
+    """BASELINE.json configs[1], the headline bench configuration (B=64, Tp=150, Tm=800, alignments returned): eight
+    rows of the SAME batch (first, last, the full-length ones, four in between) against the oracle, alignments included."""
+    sd = O.make_state_dict(41)
+    ph, mel, pl, ml = O.make_inputs(64, 150, 800, seed=42)
+    rows, ref = _oracle_rows(sd, ph, mel, pl, ml, [0, 1, 17, 31, 32, 46, 62, 63])
+    out = _model(sd)(ph, mel, pl, ml)
+    torch.cuda.synchronize()
+    _compare(_take(out, rows), ref, pl[torch.tensor(rows)], f"cfg2 rows {rows}")
+
+
+def test_cfg5_b16_rows_vs_oracle():
+    """BASELINE.json configs[4] at B=16 (Tp=400, Tm=2000: the streaming attention kernel with the probability sweep):
+    four rows of the same batch against the oracle."""
+    sd = O.make_state_dict(51)
+    ph, mel, pl, ml = O.make_inputs(16, 400, 2000, seed=52)
+    rows, ref = _oracle_rows(sd, ph, mel, pl, ml, [0, 7, 15])
+    out = _model(sd)(ph, mel, pl, ml)
+    torch.cuda.synchronize()
+    _compare(_take(out, rows), ref, pl[torch.tensor(rows)], f"cfg5 B16 rows {rows}")
+
+
 def test_full_size_properties_cfg2():
     """BASELINE.json config 2 (B=64, Tp=150, Tm=800, alignments returned): too big for the CPU oracle inside
     the test budget, so check size-independent properties: rows of every alignment map sum to 1, carry no

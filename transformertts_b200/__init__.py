@@ -4,6 +4,7 @@
 hand-written CUDA for sm_100a behind the C ABI of include/tts_b200.h.
 """
 from .api import TransformerTTS  # noqa: F401
+from .loss import TransformerTTSLoss  # noqa: F401
 from . import _ext  # noqa: F401
 
-__all__ = ["TransformerTTS"]
+__all__ = ["TransformerTTS", "TransformerTTSLoss"]

@@ -60,6 +60,10 @@ SIGNATURES = {
                              C.c_int, C.c_int, vp]),
     "tts_decode_max_clusters": (C.c_int, [C.c_int, C.c_int]),
     "tts_postnet": (C.c_int, [C.POINTER(Weights), vp, C.c_int, C.c_int, vp, vp, C.c_size_t, vp]),
+    "tts_teacher_forcing_mix": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]),
+    "tts_loss_scratch_bytes": (C.c_size_t, []),
+    "tts_loss": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp, vp, C.c_size_t, vp]),
+    "tts_pack_outputs": (C.c_int, [vp, vp, vp, C.c_longlong, vp, vp]),
     "tts_op_linear": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_int, vp, vp, vp,
                                 vp, vp, vp]),
     "tts_op_conv1d": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]),
@@ -83,7 +87,7 @@ def load():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)
             fn.restype, fn.argtypes = res, args
-        if lib.tts_abi_version() != 2:
+        if lib.tts_abi_version() != 3:
             raise RuntimeError("libtts_b200.so ABI version mismatch")
         _lib = lib
     return _lib

@@ -18,7 +18,7 @@ import torch.nn as nn
 from . import _ext
 from .weights import D, FFN, KS, MAX_PE, N_MELS, PackedWeights
 
-FLAG_WANT_ALIGN, FLAG_ENC_MASK, FLAG_SERIAL = 1, 2, 4
+FLAG_WANT_ALIGN, FLAG_ENC_MASK, FLAG_SERIAL, FLAG_MEL_BF16 = 1, 2, 4, 8
 
 
 class _Holder(nn.Module):
@@ -131,6 +131,8 @@ class TransformerTTS(nn.Module):
         for key, t in _reference_layout_init(n_phon).items():
             self._register(key, t.to(self.device))
         self._packed: Optional[PackedWeights] = None
+        self._packed_fp = None
+        self._fp_tensors = None
         self._ws = None
         self.register_load_state_dict_post_hook(lambda module, incompatible: module.refresh_weights())
 
@@ -157,12 +159,30 @@ class TransformerTTS(nn.Module):
 
     def refresh_weights(self):
         """Drop the packed (bf16 / BN-folded) device copies; they are rebuilt from the parameters on next use."""
-        self._packed = None
+        self._packed, self._fp_tensors = None, None
+
+    def _fingerprint(self):
+        """(data_ptr, in-place version counter) of every parameter and buffer: changes whenever a tensor is replaced,
+        moved or updated in place (optimizer step, `.data.fill_()`, BN statistic edits)."""
+        if self._fp_tensors is None:      # the module-tree walk is the slow part: keep the flat list
+            self._fp_tensors = list(self.parameters()) + list(self.buffers())
+        return tuple((t.data_ptr(), t._version) for t in self._fp_tensors)
 
     def _weights(self) -> PackedWeights:
-        if self._packed is None:
+        fp = self._fingerprint()
+        if self._packed is None or self._packed_fp != fp:
             self._packed = PackedWeights(self.state_dict(), self.device)
+            self._packed_fp = fp
         return self._packed
+
+    def _apply(self, fn, *args, **kwargs):
+        """`.to()` / `.cuda()` / `.float()`: keep `self.device` in step with the parameters and drop the packed copies."""
+        out = super()._apply(fn, *args, **kwargs)
+        dev = self.emb.weight.device
+        if dev.type == "cuda":
+            self.device = dev
+        self._packed, self._ws, self._fp_tensors = None, None, None
+        return out
 
     def _workspace(self, B, Tp, Tm):
         need = _ext.load().tts_workspace_bytes(B, Tp, Tm) + 1024
@@ -185,7 +205,10 @@ class TransformerTTS(nn.Module):
                                "statistics); call .eval() first. Training-mode forward/backward is out of scope.")
         lib = _ext.load()
         phoneme, phoneme_lens = self._prep(phoneme, torch.int64), self._prep(phoneme_lens, torch.int64)
-        melspec, melspec_lens = self._prep(melspec, torch.float32), self._prep(melspec_lens, torch.int64)
+        # the target mel may arrive as bf16 (data.collate_fn(mel_dtype=bfloat16)): half the H2D bytes, no cast kernel
+        mel_bf16 = melspec.dtype == torch.bfloat16
+        melspec = self._prep(melspec, torch.bfloat16 if mel_bf16 else torch.float32)
+        melspec_lens = self._prep(melspec_lens, torch.int64)
         if phoneme.dim() != 2 or melspec.dim() != 3 or melspec.shape[2] != N_MELS:
             raise ValueError("expected phoneme [B,Tp] and melspec [B,Tm,80]")
         B, Tp = phoneme.shape
@@ -197,11 +220,13 @@ class TransformerTTS(nn.Module):
         with torch.cuda.device(self.device):
             w = self._weights()
             ws, ws_bytes = self._workspace(B, Tp, Tm)
-            pred = torch.empty(B, Tm, N_MELS, dtype=torch.float32, device=self.device)
-            post = torch.empty_like(pred)
-            stop = torch.empty(B, Tm, dtype=torch.float32, device=self.device)
+            # pred | post | stop back to back in ONE allocation: a consumer on the host fetches them with one copy
+            n = B * Tm * N_MELS
+            flat = torch.empty(2 * n + B * Tm, dtype=torch.float32, device=self.device)
+            pred, post, stop = flat[:n].view(B, Tm, N_MELS), flat[n:2 * n].view(B, Tm, N_MELS), flat[2 * n:].view(B, Tm)
             align = torch.empty(3, B, 4, Tm, Tp, dtype=torch.float32, device=self.device) if return_alignments else None
-            flags = FLAG_ENC_MASK | (FLAG_WANT_ALIGN if return_alignments else 0) | (FLAG_SERIAL if self.serial_encoder else 0)
+            flags = (FLAG_ENC_MASK | (FLAG_WANT_ALIGN if return_alignments else 0) |
+                     (FLAG_SERIAL if self.serial_encoder else 0) | (FLAG_MEL_BF16 if mel_bf16 else 0))
             _ext.check(lib.tts_forward(C.byref(w.struct), _ext.ptr(phoneme), _ext.ptr(melspec), _ext.ptr(phoneme_lens),
                                        _ext.ptr(melspec_lens), B, Tp, Tm, flags, _ext.ptr(pred), _ext.ptr(post),
                                        _ext.ptr(stop), _ext.ptr(align), ws, ws_bytes, self._stream()), "tts_forward")

@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libtts_b200.so")
-SOURCES = ["gemm.cu", "gemm2.cu", "ffn.cu", "attention.cu", "attention2.cu", "attention3.cu", "decode.cu", "c_api.cu"]
+SOURCES = ["host.cu", "gemm2.cu", "ffn.cu", "attention2.cu", "attention3.cu", "decode.cu", "train_aux.cu", "c_api.cu"]
 HEADERS = ["ptx.cuh", "kernels.h", "decode.cuh", os.path.join("..", "..", "include", "tts_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math" if os.environ.get("TTS_FAST_MATH") else "-DTTS_EXACT_MATH"]

@@ -360,17 +360,11 @@ bool attn2_supports(const AttnArgs& a) {
 }
 
 const char* attn2_launch(const AttnArgs& a, cudaStream_t s) {
-  static bool attr_done = false;
-  static int sm_count = 0;
-  if (!attr_done) {
-    if (cudaFuncSetAttribute(attn2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TOTAL) != cudaSuccess)
-      return "cudaFuncSetAttribute(attention2) failed";
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
-      return "attention2: cannot query the SM count";
-    attr_done = true;
-  }
+  static PerDeviceOnce once;
+  DevInfo di;
+  if (const char* e = device_info(&di)) return e;
+  if (const char* e = ensure_smem(attn2_kernel, TOTAL, once, di.dev, "cudaFuncSetAttribute(attention2) failed")) return e;
+  const int sm_count = di.sm_count;
   CUtensorMap tmQ, tmK, tmV;
   // each map covers one head's 64 columns at a time: dims (row pitch in elements, rows, batch)
   const char* e = make_tmap_3d(&tmQ, a.Q, (uint64_t)kD, (uint64_t)a.Tq, (uint64_t)a.B, (uint64_t)a.ldq * 2,

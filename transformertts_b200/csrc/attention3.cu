@@ -294,13 +294,11 @@ bool attn3_supports(const AttnArgs& a) {
 
 const char* attn3_launch(const AttnArgs& a, cudaStream_t s) {
   const int NT = (a.Tk + 63) / 64;
-  static int attr_bytes = 0;
+  static PerDeviceOnce once;
+  DevInfo di;
+  if (const char* e = device_info(&di)) return e;
+  if (const char* e = ensure_smem(attn3_kernel, smem_total(4), once, di.dev, "cudaFuncSetAttribute(attention3) failed")) return e;
   const int bytes = smem_total(NT);
-  if (bytes > attr_bytes) {
-    if (cudaFuncSetAttribute(attn3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_total(4)) != cudaSuccess)
-      return "cudaFuncSetAttribute(attention3) failed";
-    attr_bytes = smem_total(4);
-  }
   CUtensorMap tmQ, tmK, tmV;
   const char* e = make_tmap_3d(&tmQ, a.Q, (uint64_t)kD, (uint64_t)a.Tq, (uint64_t)a.B, (uint64_t)a.ldq * 2,
                                (uint64_t)a.Tq * a.ldq * 2, 64, BQ);

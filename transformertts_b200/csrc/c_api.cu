@@ -1,6 +1,6 @@
 // extern "C" boundary (include/tts_b200.h) and the orchestration of the hot path:
 // TransformerTTS.forward (model/model.py:260-320) and .inference (model/model.py:323-394) as sequences
-// of the kernels in gemm.cu / attention.cu / decode.cu over a caller-provided workspace.
+// of the kernels in gemm2.cu / ffn.cu / attention2.cu / attention3.cu / decode.cu over a caller-provided workspace.
 #include "../../include/tts_b200.h"
 
 #include <math.h>
@@ -350,7 +350,7 @@ static SideStream* side_stream() {
 }
 
 // ------------------------------------------------------------------ TransformerTTS.forward
-extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const float* mel, const int64_t* ph_lens,
+extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const void* mel, const int64_t* ph_lens,
                            const int64_t* mel_lens, int B, int Tp, int Tm, int flags, float* mel_pre, float* mel_post,
                            float* stop, float* align, void* workspace, size_t ws_bytes, void* stream) {
   if (check_common(w, B, Tp, Tm, workspace, ws_bytes)) return 1;
@@ -386,9 +386,15 @@ extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const fl
   if (enc_err != nullptr) return fail(enc_err);
 
   // decoder prenet on the go-frame-shifted target (model/model.py:278-279, 297): frame t reads mel[t-1]
-  TRY(cast_mel_launch(mel, ws.mel_in, (size_t)Nm * kMel, s));
+  const bf16* mel16 = ws.mel_in;
+  if (flags & TTS_FLAG_MEL_BF16) {
+    if ((reinterpret_cast<uintptr_t>(mel) & 15) != 0) return fail("bf16 mel must be 16-byte aligned");
+    mel16 = reinterpret_cast<const bf16*>(mel);      // read in place by the prenet's TMA loads
+  } else {
+    TRY(cast_mel_launch(reinterpret_cast<const float*>(mel), ws.mel_in, (size_t)Nm * kMel, s));
+  }
   {
-    GemmArgs g = conv_args(ws.mel_in, B, Tm, kMel, w->pre1_w, w->pre1_b, kD, 1, -1);
+    GemmArgs g = conv_args(mel16, B, Tm, kMel, w->pre1_w, w->pre1_b, kD, 1, -1);
     g.act = ACT_RELU; g.out_bf16 = ws.d0; g.ld_bf16 = kD;
     TRY(gemm_launch(g, s));
     GemmArgs h = linear_args(ws.d0, Nm, kD, w->pre2_w, w->pre2_b, kD);
@@ -500,5 +506,46 @@ extern "C" int tts_postnet(const TtsWeights* w, const float* mel_pre, int B, int
   Workspace ws = carve(workspace, B, 1, T);
   TRY(cast_mel_launch(mel_pre, ws.mel_pre16, (size_t)B * T * kMel, s));
   TRY(run_postnet(w, ws.mel_pre16, mel_pre, B, T, ws.qkv_d, ws.ffn_d, mel_post, s));
+  return 0;
+}
+
+// ------------------------------------------------------------------ forward-only training / validation helpers
+extern "C" int tts_teacher_forcing_mix(const float* pred, const float* mel, const uint8_t* seed, const int64_t* mel_lens,
+                                       int B, int T, int L_bar, float* out, void* stream) {
+  if (pred == nullptr || mel == nullptr || seed == nullptr || mel_lens == nullptr || out == nullptr)
+    return fail("tts_teacher_forcing_mix: NULL pointer");
+  if (B <= 0 || T <= 0 || L_bar <= 0) return fail("tts_teacher_forcing_mix: B, T and L_bar must be positive");
+  if (((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(mel) | reinterpret_cast<uintptr_t>(out)) & 15) != 0)
+    return fail("tts_teacher_forcing_mix: tensors must be 16-byte aligned");
+  if (out == pred || out == mel) return fail("tts_teacher_forcing_mix: out must not alias an input");
+  TRY(tf_mix_launch(pred, mel, seed, mel_lens, B, T, L_bar, out, (cudaStream_t)stream));
+  return 0;
+}
+
+extern "C" size_t tts_loss_scratch_bytes(void) {
+  DevInfo di;
+  if (device_info(&di) != nullptr) return 0;
+  return (size_t)loss_blocks(di.sm_count) * 24;
+}
+
+extern "C" int tts_loss(const float* pred, const float* post, const float* stop, const float* mel, const int64_t* mel_lens,
+                        int B, int T, float pos_weight, float* out4, void* scratch, size_t scratch_bytes, void* stream) {
+  if (pred == nullptr || post == nullptr || stop == nullptr || mel == nullptr || mel_lens == nullptr || out4 == nullptr)
+    return fail("tts_loss: NULL pointer");
+  if (B <= 0 || T <= 0) return fail("tts_loss: B and T must be positive");
+  if (((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(post) | reinterpret_cast<uintptr_t>(mel)) & 15) != 0)
+    return fail("tts_loss: tensors must be 16-byte aligned");
+  if ((reinterpret_cast<uintptr_t>(scratch) & 7) != 0) return fail("tts_loss: scratch must be 8-byte aligned");
+  TRY(loss_launch(pred, post, stop, mel, mel_lens, B, T, pos_weight, out4, scratch, scratch_bytes, (cudaStream_t)stream));
+  return 0;
+}
+
+extern "C" int tts_pack_outputs(const float* pred, const float* post, const float* stop, long long rows, void* packed,
+                                void* stream) {
+  if (pred == nullptr || post == nullptr || stop == nullptr || packed == nullptr) return fail("tts_pack_outputs: NULL pointer");
+  if (rows <= 0) return fail("tts_pack_outputs: rows must be positive");
+  if (((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(post) | reinterpret_cast<uintptr_t>(packed)) & 15) != 0)
+    return fail("tts_pack_outputs: tensors must be 16-byte aligned");
+  TRY(pack_out_launch(pred, post, stop, rows, packed, (cudaStream_t)stream));
   return 0;
 }

@@ -525,8 +525,11 @@ static int max_clusters_r(int C) {
 }
 
 int decode_max_clusters(int R, int C) {
-  static int cache[9][17] = {};
+  static int cache_dev[kMaxDevices][9][17] = {};     // per device; benign race (same value from every thread)
   if (R < 1 || R > 8 || C < 1 || C > 16) return 0;
+  DevInfo di;
+  if (device_info(&di) != nullptr) return 0;
+  int (*cache)[17] = cache_dev[di.dev];
   if (cache[R][C] == 0) {
     int n = 0;
     switch (R) {

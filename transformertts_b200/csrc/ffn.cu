@@ -376,17 +376,11 @@ bool ffn_supports(const FfnArgs& a) {
 }
 
 const char* ffn_launch(const FfnArgs& a, cudaStream_t s) {
-  static bool attr_done = false;
-  static int sm_count = 0;
-  if (!attr_done) {
-    if (cudaFuncSetAttribute(ffn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TOTAL) != cudaSuccess)
-      return "cudaFuncSetAttribute(ffn) failed";
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
-      return "ffn: cannot query the SM count";
-    attr_done = true;
-  }
+  static PerDeviceOnce once;
+  DevInfo di;
+  if (const char* e = device_info(&di)) return e;
+  if (const char* e = ensure_smem(ffn_kernel, TOTAL, once, di.dev, "cudaFuncSetAttribute(ffn) failed")) return e;
+  const int sm_count = di.sm_count;
   CUtensorMap tmX, tmW1, tmW2, tmO;
   const char* e = make_tmap_3d(&tmX, a.x, kD, (uint64_t)a.M, 1, kD * 2, (uint64_t)a.M * kD * 2, BK, BM);
   if (e) return e;
@@ -400,7 +394,8 @@ const char* ffn_launch(const FfnArgs& a, cudaStream_t s) {
   p.M = a.M; p.m_tiles = (a.M + BM - 1) / BM;
   p.b1 = a.b1; p.b2 = a.b2; p.ln_g = a.ln_g; p.ln_b = a.ln_b;
   // clusters that can be resident at once (GPC boundaries may leave single SMs unpaired): the tile walk is sized to it
-  static int max_pairs = 0;
+  static int max_pairs_dev[kMaxDevices] = {};        // benign race: every thread computes the same value
+  int& max_pairs = max_pairs_dev[di.dev];
   if (max_pairs == 0) {
     cudaLaunchConfig_t q = {};
     q.gridDim = dim3(2 * (sm_count / 2)); q.blockDim = dim3(THREADS); q.dynamicSmemBytes = TOTAL;

@@ -495,25 +495,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 }
 
 // ------------------------------------------------------------------ host side
-static int g_sm_count = 0;
-
 template <bool LN, bool WS, bool F32 = false, bool PAIR = false>
 static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
                            const CUtensorMap& tmR, const Dev& p, cudaStream_t s) {
   using P = Plan<LN, WS, F32, PAIR>;
-  static bool attr_done = false;
-  if (!attr_done) {
-    if (cudaFuncSetAttribute(gemm2_kernel<LN, WS, F32, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::TOTAL) !=
-        cudaSuccess)
-      return "cudaFuncSetAttribute(gemm2) failed";
-    attr_done = true;
-  }
-  if (g_sm_count == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || g_sm_count <= 0)
-      return "gemm2: cannot query the SM count";
-  }
+  static PerDeviceOnce once;
+  DevInfo di;
+  if (const char* e = device_info(&di)) return e;
+  if (const char* e = ensure_smem(gemm2_kernel<LN, WS, F32, PAIR>, P::TOTAL, once, di.dev, "cudaFuncSetAttribute(gemm2) failed"))
+    return e;
+  const int g_sm_count = di.sm_count;
   cudaError_t err;
   if (PAIR) {
     const int units = ((p.m_tiles + 1) / 2) * p.n_tiles;   // list entries: pairs of m-tiles

@@ -22,6 +22,28 @@ constexpr int kPeMax = 5000; // model/model.py:76
 
 void note_launch(int n = 1);      // counts kernel launches (tts_launch_count in the C ABI)
 
+// Per-device host state (host.cu).  Function attributes (the > 48 KB shared-memory opt-in) and the SM count belong to
+// a DEVICE, and one process may drive several GPUs, so every launcher keys them by the current device ordinal.
+constexpr int kMaxDevices = 64;
+struct DevInfo { int dev; int sm_count; };
+const char* device_info(DevInfo* out);            // current device + its SM count (cached); nullptr or an error string
+class PerDeviceOnce {                              // "has this kernel's attribute been set on device d yet"
+ public:
+  bool need(int dev);
+  void mark(int dev);
+ private:
+  bool done_[kMaxDevices] = {};
+};
+// Opt a kernel into `bytes` of dynamic shared memory once per device.
+template <class K>
+inline const char* ensure_smem(K kernel, int bytes, PerDeviceOnce& once, int dev, const char* what) {
+  if (once.need(dev)) {
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return what;
+    once.mark(dev);
+  }
+  return nullptr;
+}
+
 enum Act { ACT_NONE = 0, ACT_RELU = 1, ACT_TANH = 2 };
 
 // One dense contraction  out[row, n] = epi( sum_k A[row(+tap), k] * W[n, k] ).
@@ -86,6 +108,15 @@ const char* embed_launch(const int64_t* phoneme, const bf16* table, bf16* out, i
                          cudaStream_t s);
 const char* cast_mel_launch(const float* mel, bf16* out, size_t n, cudaStream_t s);
 const char* lens_launch(const int64_t* in, int* out, int n, int lo, int hi, cudaStream_t s);
+
+// forward-only training / validation helpers (train_aux.cu)
+const char* tf_mix_launch(const float* pred, const float* mel, const uint8_t* seed, const int64_t* lens, int B, int T,
+                          int L_bar, float* out, cudaStream_t s);
+int loss_blocks(int sm_count);                                 // partial sums the loss keeps in its scratch (24 B each)
+const char* loss_launch(const float* pred, const float* post, const float* stop, const float* mel, const int64_t* lens,
+                        int B, int T, float pos_weight, float* out4, void* scratch, size_t scratch_bytes, cudaStream_t s);
+const char* pack_out_launch(const float* pred, const float* post, const float* stop, long long rows, void* out,
+                            cudaStream_t s);
 
 // Launch with programmatic stream serialization: the kernel's prologue (barrier init, TMEM allocation, tensor-map
 // prefetch) may overlap the tail of the previous kernel in the stream; the kernel itself calls griddepcontrol.wait

@@ -1,6 +1,6 @@
 // Thin inline-PTX wrappers for sm_100a: mbarrier, TMA (cp.async.bulk.tensor), tcgen05 (MMA,
 // TMEM alloc/ld, commit) and the UMMA shared-memory / instruction descriptors.
-// Everything here is device-side plumbing shared by gemm.cu and attention.cu.
+// Everything here is device-side plumbing shared by the kernel translation units.
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>

@@ -1,0 +1,273 @@
+"""Input / output boundary of the hot path: the reference's `collate_fn` (dataset.py:71-102) and
+`prepare_batch` (utils/util.py:96-100) as a pinned, double-buffered host <-> device pipeline, plus length bucketing.
+
+* `collate_fn(batch)`             same dict as the reference's (rows sorted by phoneme length descending, zero padded,
+                                  Tp / Tm = longest row); optional bf16 mel (halves the host -> device bytes; the
+                                  kernels round the target mel to bf16 anyway) and reusable pinned staging buffers.
+* `bucket_batches(...)`           batches of similar mel length: the forward runs over the padded rectangle
+                                  (SURVEY F11), so valid / padded frames is throughput; random batches of LJSpeech-shaped
+                                  lengths sit near 0.8, bucketed ones above 0.95.
+* `PinnedFeeder`                  step i+1's inputs travel host -> device on a copy stream while step i computes.
+* `OutputFetcher`                 step i's results travel device -> host on another stream while step i+1 computes:
+                                  ONE copy per step (pred / post / stop share one allocation), optionally packed to bf16
+                                  on the device first (`tts_pack_outputs`) at half the bytes.
+Everything here is host plumbing around torch tensors and CUDA streams; the arithmetic stays in libtts_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Iterable, Iterator, List, Optional, Sequence
+
+import torch
+
+from . import _ext
+
+N_MELS = 80
+KEYS = ("phoneme", "melspec", "phoneme_lens", "melspec_lens")
+
+
+# ---------------------------------------------------------------------------------------------- collate
+def collate_fn(batch: Sequence[dict], mel_dtype: torch.dtype = torch.float32, pin: bool = False) -> Dict[str, object]:
+    """dataset.py:71-102.  `batch`: list of {'phoneme': LongTensor[Lp], 'melspec': FloatTensor[Lm, n_mels],
+    'transcript': str}.  Returns phoneme [B,Tp] i64, melspec [B,Tm,n_mels], phoneme_lens / melspec_lens [B] i64,
+    transcript list -- rows sorted by phoneme length, longest first (stable, like torch.argsort on equal keys is not:
+    ties keep the reference's order by using the same call)."""
+    phoneme_lens = torch.tensor([len(s["phoneme"]) for s in batch])
+    order = torch.argsort(phoneme_lens, descending=True)                       # :74-76
+    batch = [batch[int(i)] for i in order]
+    Tp = int(phoneme_lens[order[0]])                                           # :78
+    Tm = max(int(s["melspec"].shape[0]) for s in batch)                        # :79
+    n_mels = int(batch[0]["melspec"].shape[1])
+    B = len(batch)
+    mk = (lambda *shape, dtype: torch.zeros(*shape, dtype=dtype).pin_memory()) if pin else \
+         (lambda *shape, dtype: torch.zeros(*shape, dtype=dtype))
+    phoneme = mk(B, Tp, dtype=torch.long)                                      # :83-85
+    melspec = mk(B, Tm, n_mels, dtype=mel_dtype)
+    melspec_lens = mk(B, dtype=torch.long)
+    transcripts: List[str] = []
+    for i, s in enumerate(batch):                                              # :88-96
+        lp, lm = len(s["phoneme"]), int(s["melspec"].shape[0])
+        phoneme[i, :lp] = s["phoneme"]
+        melspec[i, :lm, :] = s["melspec"]
+        melspec_lens[i] = lm
+        transcripts.append(s.get("transcript", ""))
+    pl = phoneme_lens[order]
+    return {"phoneme": phoneme, "melspec": melspec, "phoneme_lens": pl.pin_memory() if pin else pl,
+            "melspec_lens": melspec_lens, "transcript": transcripts}            # :98-104
+
+
+# ---------------------------------------------------------------------------------------------- length bucketing
+def bucket_batches(mel_lens: Sequence[int], batch_size: int, shuffle: bool = False, bucket_factor: int = 50,
+                   generator: Optional[torch.Generator] = None, drop_last: bool = False) -> List[List[int]]:
+    """Index lists of batches whose utterances have similar mel length.  Utterances are (optionally) shuffled, cut into
+    pools of `bucket_factor * batch_size`, each pool sorted by mel length and cut into consecutive batches; the batch order
+    is shuffled again when `shuffle`.  With shuffle=False and bucket_factor large it is a plain sort (validation)."""
+    n = len(mel_lens)
+    lens = torch.as_tensor(list(mel_lens))
+    idx = torch.randperm(n, generator=generator) if shuffle else torch.arange(n)
+    pool = max(batch_size, bucket_factor * batch_size)
+    batches: List[List[int]] = []
+    for s in range(0, n, pool):
+        chunk = idx[s:s + pool]
+        chunk = chunk[torch.argsort(lens[chunk], descending=True, stable=True)]
+        for t in range(0, len(chunk), batch_size):
+            b = chunk[t:t + batch_size].tolist()
+            if len(b) == batch_size or not drop_last:
+                batches.append(b)
+    if shuffle:
+        perm = torch.randperm(len(batches), generator=generator).tolist()
+        batches = [batches[i] for i in perm]
+    return batches
+
+
+def padding_efficiency(mel_lens: Sequence[int], batches: Sequence[Sequence[int]]) -> float:
+    """valid frames / padded frames over a set of batches (each batch is padded to its own longest utterance)."""
+    lens = list(mel_lens)
+    valid = sum(lens[i] for b in batches for i in b)
+    padded = sum(len(b) * max(lens[i] for i in b) for b in batches)
+    return valid / max(padded, 1)
+
+
+# ---------------------------------------------------------------------------------------------- host -> device
+class PinnedFeeder:
+    """Double-buffered feed of collated batches to the device.
+
+        for batch in PinnedFeeder(loader, device):        # dict of device tensors (+ 'transcript')
+            out = model(batch['phoneme'], batch['melspec'], batch['phoneme_lens'], batch['melspec_lens'])
+
+    While the consumer computes on batch i, batch i+1 is staged into pinned host memory (if it is not pinned already)
+    and copied on a private stream; the consumer's stream waits on the copy's event, and a slot's device buffers are
+    reused only after the consumer's work that read them has been recorded as finished."""
+
+    def __init__(self, batches: Iterable[dict], device, depth: int = 2, mel_dtype: Optional[torch.dtype] = None):
+        self.batches, self.device, self.depth, self.mel_dtype = batches, torch.device(device), max(2, depth), mel_dtype
+        self.copy_stream = torch.cuda.Stream(self.device)
+        self._pinned: List[Dict[str, torch.Tensor]] = [dict() for _ in range(self.depth)]
+        self._dev: List[Dict[str, torch.Tensor]] = [dict() for _ in range(self.depth)]
+        self._consumed: List[Optional[torch.cuda.Event]] = [None] * self.depth
+        self._copied: List[Optional[torch.cuda.Event]] = [None] * self.depth
+        self.h2d_bytes = 0                                   # bytes of the most recent batch
+
+    @staticmethod
+    def _fit(store: Dict[str, torch.Tensor], key: str, like: torch.Tensor, dtype, make):
+        t = store.get(key)
+        n = like.numel()
+        if t is None or t.dtype != dtype or t.numel() < n:
+            t = make(max(n, 1), dtype)
+            store[key] = t
+        return t[:n].view(like.shape)
+
+    def _stage(self, slot: int, batch: dict):
+        ev = self._consumed[slot]
+        if self._copied[slot] is not None:
+            self._copied[slot].synchronize()                 # the slot's pinned staging buffers have been read out
+        dev_batch: Dict[str, object] = {"transcript": batch.get("transcript")}
+        nbytes = 0
+        with torch.cuda.stream(self.copy_stream):
+            if ev is not None:
+                self.copy_stream.wait_event(ev)              # device buffers of this slot are free
+            for k in KEYS:
+                src = batch[k]
+                dtype = self.mel_dtype if (k == "melspec" and self.mel_dtype is not None) else src.dtype
+                if not (src.is_pinned() and src.dtype == dtype and src.is_contiguous()):
+                    pin = self._fit(self._pinned[slot], k, src, dtype,
+                                    lambda n, dt: torch.empty(n, dtype=dt).pin_memory())
+                    pin.copy_(src)                           # host-side cast / gather into pinned memory
+                    src = pin
+                dst = self._fit(self._dev[slot], k, src, dtype,
+                                lambda n, dt: torch.empty(n, dtype=dt, device=self.device))
+                dst.copy_(src, non_blocking=True)
+                dev_batch[k] = dst
+                nbytes += src.numel() * src.element_size()
+            ready = torch.cuda.Event()
+            ready.record(self.copy_stream)
+        self._copied[slot] = ready
+        self.h2d_bytes = nbytes
+        return dev_batch, ready
+
+    def __iter__(self) -> Iterator[dict]:
+        it = iter(self.batches)
+        pending = []                                         # (slot, device batch, ready event)
+        slot = 0
+        try:
+            first = next(it)
+        except StopIteration:
+            return
+        pending.append((slot, *self._stage(slot, first)))
+        while pending:
+            cur_slot, cur, ready = pending.pop(0)
+            nxt = next(it, None)
+            if nxt is not None:                              # issue the next copy before handing out the current batch
+                slot = (slot + 1) % self.depth
+                pending.append((slot, *self._stage(slot, nxt)))
+            torch.cuda.current_stream(self.device).wait_event(ready)
+            yield cur
+            done = torch.cuda.Event()
+            done.record(torch.cuda.current_stream(self.device))
+            self._consumed[cur_slot] = done
+
+
+# ---------------------------------------------------------------------------------------------- device -> host
+class OutputFetcher:
+    """Copies each step's pred / post / stop to pinned host memory on a private stream, one copy per step.
+
+        fetch = OutputFetcher(device, dtype=torch.float32)      # or torch.bfloat16: packed on the device first
+        h = fetch(out)            # enqueue; returns the slot's host views (valid after fetch.wait() / next reuse)
+
+    `forward` allocates the three outputs back to back in one buffer, so the fp32 path is a single cudaMemcpyAsync of
+    B*Tm*161 floats; the bf16 path runs `tts_pack_outputs` (one streaming kernel) into [B*Tm][168] bf16 and copies that."""
+
+    def __init__(self, device, depth: int = 2, dtype: torch.dtype = torch.float32, with_alignments: bool = False):
+        if dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError("dtype must be float32 or bfloat16")
+        self.device, self.depth, self.dtype, self.with_alignments = torch.device(device), max(2, depth), dtype, with_alignments
+        self.stream = torch.cuda.Stream(self.device)
+        self._host: List[Dict[str, torch.Tensor]] = [dict() for _ in range(self.depth)]
+        self._dev16: List[Optional[torch.Tensor]] = [None] * self.depth
+        self._done: List[Optional[torch.cuda.Event]] = [None] * self.depth
+        self._i = 0
+        self.d2h_bytes = 0
+
+    def _host_buf(self, slot, key, n, dtype):
+        t = self._host[slot].get(key)
+        if t is None or t.numel() < n or t.dtype != dtype:
+            t = torch.empty(max(n, 1), dtype=dtype).pin_memory()
+            self._host[slot][key] = t
+        return t[:n]
+
+    @staticmethod
+    def _flat_f32(out):
+        """One flat fp32 view over pred | post | stop when they sit back to back in one allocation (api.forward)."""
+        pred, post, stop = out["pred_melspec"], out["post_melspec"], out["pred_stop"]
+        if not (pred.is_contiguous() and post.is_contiguous() and stop.is_contiguous()):
+            return None
+        if post.data_ptr() != pred.data_ptr() + pred.numel() * 4 or stop.data_ptr() != post.data_ptr() + post.numel() * 4:
+            return None
+        if pred.untyped_storage().data_ptr() != stop.untyped_storage().data_ptr():
+            return None
+        total = pred.numel() + post.numel() + stop.numel()
+        return torch.empty(0, dtype=torch.float32, device=pred.device).set_(pred.untyped_storage(), pred.storage_offset(),
+                                                                            (total,), (1,))
+
+    def __call__(self, out: Dict[str, object]) -> Dict[str, torch.Tensor]:
+        slot = self._i % self.depth
+        self._i += 1
+        if self._done[slot] is not None:
+            self._done[slot].synchronize()                   # the host buffers of this slot have been filled (and read)
+        pred, post, stop = out["pred_melspec"], out["post_melspec"], out["pred_stop"]
+        B, T, _ = pred.shape
+        rows = B * T
+        produced = torch.cuda.Event()
+        produced.record(torch.cuda.current_stream(self.device))
+        res: Dict[str, torch.Tensor] = {}
+        nbytes = 0
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(produced)
+            if self.dtype == torch.bfloat16:
+                d16 = self._dev16[slot]
+                if d16 is None or d16.numel() < rows * 168:
+                    d16 = torch.empty(rows * 168, dtype=torch.bfloat16, device=self.device)
+                    self._dev16[slot] = d16
+                _ext.check(_ext.load().tts_pack_outputs(_ext.ptr(pred), _ext.ptr(post), _ext.ptr(stop), rows, _ext.ptr(d16),
+                                                        C.c_void_p(self.stream.cuda_stream)), "tts_pack_outputs")
+                h = self._host_buf(slot, "packed", rows * 168, torch.bfloat16)
+                h.copy_(d16[:rows * 168], non_blocking=True)
+                nbytes += rows * 168 * 2
+                hv = h.view(B, T, 168)
+                res = {"pred_melspec": hv[:, :, :80], "post_melspec": hv[:, :, 80:160], "pred_stop": hv[:, :, 160]}
+            else:
+                flat = self._flat_f32(out)
+                if flat is not None:
+                    h = self._host_buf(slot, "packed", flat.numel(), torch.float32)
+                    h.copy_(flat, non_blocking=True)
+                    nbytes += flat.numel() * 4
+                    n = rows * 80
+                    res = {"pred_melspec": h[:n].view(B, T, 80), "post_melspec": h[n:2 * n].view(B, T, 80),
+                           "pred_stop": h[2 * n:].view(B, T)}
+                else:
+                    for k in ("pred_melspec", "post_melspec", "pred_stop"):
+                        h = self._host_buf(slot, k, out[k].numel(), torch.float32)
+                        h.copy_(out[k].reshape(-1), non_blocking=True)
+                        nbytes += out[k].numel() * 4
+                        res[k] = h.view(out[k].shape)
+            for t in (pred, post, stop):
+                t.record_stream(self.stream)
+            if self.with_alignments:
+                hs = []
+                for l, a in enumerate(out["alignments"]):
+                    h = self._host_buf(slot, f"align{l}", a.numel(), torch.float32)
+                    h.copy_(a.reshape(-1), non_blocking=True)
+                    a.record_stream(self.stream)
+                    nbytes += a.numel() * 4
+                    hs.append(h.view(a.shape))
+                res["alignments"] = hs
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        self._done[slot] = ev
+        self.d2h_bytes = nbytes
+        return res
+
+    def wait(self):
+        for ev in self._done:
+            if ev is not None:
+                ev.synchronize()
