@@ -106,10 +106,14 @@ int tts_encode(const TtsWeights* w, const int64_t* phoneme, const int64_t* ph_le
  * mel_out f32 [B][max_frames][80], stop_out f32 [B][max_frames]; stop_count int32 [max_frames] scratch;
  * n_frames int32 [1] (device) receives the number of frames produced under the reference's rule
  * (first step at which sigmoid(stop) >= threshold for ALL rows, else max_frames).
- * rows_per_cluster / cluster_size: 0 = choose automatically. */
+ * rows_per_cluster / cluster_size: 0 = choose automatically.
+ * forced_mel: NULL for the reference's greedy loop; else f32 [B][max_frames][80], and step t consumes frame t-1 of it
+ * instead of the kernel's own prediction (teacher-forced decode: every step is computed through the same kernel and
+ * K/V cache but errors do not compound through the feedback; used for full-horizon parity). */
 int tts_decode(const TtsWeights* w, const void* cross_kv, const int32_t* ph_len_i32, int B, int Tp,
                int max_frames, float stop_threshold, void* self_kv, float* mel_out, float* stop_out,
-               int32_t* stop_count, int32_t* n_frames, int rows_per_cluster, int cluster_size, void* stream);
+               int32_t* stop_count, int32_t* n_frames, int rows_per_cluster, int cluster_size,
+               const float* forced_mel, void* stream);
 
 /* Number of thread-block clusters of the decode kernel the current device holds at once for a given plan
  * (cudaOccupancyMaxActiveClusters); 0 if the plan cannot run. */

@@ -4,8 +4,11 @@ produced (tests/golden, oracle/make_golden.py).
 
 Stated tolerance (BASELINE.json north_star: "within a stated tolerance ... BF16 inputs and FP32 accumulate"):
 activations are rounded to bf16 between kernels, so against the fp32 reference on bf16-rounded weights we
-gate   mel_pre / mel_post: max-abs <= MEL_ATOL and relative L2 <= MEL_REL_L2;   stop logits: max-abs <= STOP_ATOL;
-cross-attention maps: max-abs <= ALIGN_ATOL, rows sum to 1 +- 1e-3, exactly 0 on padded keys."""
+gate   mel_pre: max-abs <= PRE_ATOL, mel_post: max-abs <= POST_ATOL, both relative L2 <= MEL_REL_L2;   stop logits:
+max-abs <= STOP_ATOL;   cross-attention maps: max-abs <= ALIGN_ATOL, rows sum to 1 +- 1e-3, exactly 0 on padded keys.
+The gates are <= 1.5 x the maxima observed on B200 over every configuration below (round 2: mel_pre 0.052, mel_post
+0.135, stop 0.054, alignments 5.3e-3, rel-L2 6.1e-3 / 9.8e-3; per-config table in BASELINE.md), which sit at what a
+full-bf16 torch run of the reference itself gives (0.061 / 0.117 / 0.052 / 1.7e-3)."""
 import os
 
 import numpy as np
@@ -17,7 +20,7 @@ from parity_common import DEV, report
 
 pytestmark = pytest.mark.gpu
 
-MEL_ATOL, MEL_REL_L2, STOP_ATOL, ALIGN_ATOL = 0.15, 2e-2, 0.10, 6e-3
+PRE_ATOL, POST_ATOL, MEL_REL_L2, STOP_ATOL, ALIGN_ATOL = 0.08, 0.18, 1.5e-2, 0.08, 6e-3
 
 
 def _model(sd):
@@ -27,7 +30,7 @@ def _model(sd):
 
 def _compare(out, ref, pl, tag):
     msgs, ok_all = [], True
-    for k, atol in (("pred_melspec", MEL_ATOL), ("post_melspec", MEL_ATOL), ("pred_stop", STOP_ATOL)):
+    for k, atol in (("pred_melspec", PRE_ATOL), ("post_melspec", POST_ATOL), ("pred_stop", STOP_ATOL)):
         ok, msg = report(f"{tag} {k}", out[k], torch.as_tensor(ref[k]), atol)
         msgs.append(msg); ok_all &= ok
         if k != "pred_stop":
@@ -90,7 +93,7 @@ def test_forward_without_alignments_matches_with():
     # storing the probabilities selects the single-pass cross-attention kernel, not storing them the streaming
     # one: same math, different rounding points (bf16 P), so the outputs agree to bf16 noise, not bit for bit
     for k in ("pred_melspec", "post_melspec", "pred_stop"):
-        assert float((a[k] - b[k]).abs().max()) <= 0.15, k      # the stated forward tolerance
+        assert float((a[k] - b[k]).abs().max()) <= POST_ATOL, k      # the stated forward tolerance
     c = m(ph, mel, pl, ml, return_alignments=False)
     torch.cuda.synchronize()
     for k in ("pred_melspec", "post_melspec", "pred_stop"):

@@ -110,65 +110,113 @@ def test_inference_matches_forward_on_unpadded_batch():
 
 
 # ------------------------------------------------------------------ the benchmarked horizon: 1000 frames (configs[2])
-# One never-stopping oracle trajectory per batch size serves both tests below: the stop logit is not fed back, so the
-# planted-stop run is the same trajectory cut at the planted step (PostNet recomputed over the cut prefix).
+# At random init the AR map is chaotic over this horizon: the REFERENCE ITSELF, with its encoder output perturbed by
+# 1e-6, is 2e-2 away from its own trajectory at frame 1000, and 1.6 away for a 1e-4 perturbation (measured with the
+# oracle; table in BASELINE.md).  A bf16 K/V cache (2^-9 relative rounding) therefore cannot stay on the fp32
+# trajectory for 1000 free-running frames, and no implementation that rounds anywhere can.  So the full horizon is
+# pinned in two ways:
+#   * free-running: the drift is printed per 100-frame bucket for B=1 / B=32 and gated where it is still rounding-level
+#     for every row (the rows of a batch lose the reference trajectory at different times: the B=1 utterance stays within
+#     0.03 for 400 frames, some rows of the ragged B=32 batch leave after ~80); a free-running planted stop at frame 356
+#     (B=1) must give the identical stop index and trajectory;
+#   * teacher-forced decode (tts_decode's `forced_mel`): every one of the 1000 steps runs through the same persistent
+#     kernel and K/V cache but consumes the ORACLE's previous frame, so errors cannot compound through the feedback:
+#     all 1000 frames and stop logits are compared one step ahead, and a stop planted at frame 859 of the horizon
+#     (margin 0.34) must be found at the identical index.
 _LONG = {}
 LONG_SEED, LONG_MIN_T = 221, 800     # found by oracle search: the stop logit makes a new maximum at frame 859, margin 0.34
-# Observed drift at 1000 frames is printed per 100-frame bucket; gates are the AR tolerances above.
+FREE_GATE_FRAMES = {1: 300, 32: 50}  # free-running frames gated at the AR tolerances above
+# one-step-ahead over 1000 frames (bf16 K/V cache + bf16 cross K/V): observed on B200 pred 0.0057 / stop 0.0039 / post 0.075
+FORCED_PRE_ATOL, FORCED_STOP_ATOL, FORCED_POST_ATOL = 0.009, 0.006, 0.11
 
 
-def _long_case(B, replicate=False):
-    """replicate: all B rows are the B=1 utterance (a late all-rows crossing with margin does not occur by chance for 32
-    independent rows: the minimum over rows of 32 random logit tracks has no late record); the rows still go through the
-    batch-32 decode plan and its cross-cluster stop counting.  The drift test uses a real ragged batch."""
-    key = (B, replicate)
-    if key not in _LONG:
+def _long_case(B):
+    if B not in _LONG:
         sd = O.make_state_dict(LONG_SEED, stop_bias=-1e4)
-        if replicate:
-            ph, _, pl, _ = O.make_inputs(1, 150, 8, seed=LONG_SEED + 1)
-            ph, pl = ph.repeat(B, 1), pl.repeat(B)
-            one = _long_case(1)[3]
-            ref = {k: v.repeat(B, 1, 1) for k, v in one.items()}
-        else:
-            ph, _, pl, _ = O.make_inputs(B, 150, 8, seed=LONG_SEED + 1)
-            ref = O.inference_cached(sd, ph, pl, max_len=1001)
+        ph, _, pl, _ = O.make_inputs(B, 150, 8, seed=LONG_SEED + 1)
+        ref = O.inference_cached(sd, ph, pl, max_len=1001)
         assert ref["pred_melspec"].shape[1] == 1000
-        _LONG[key] = (sd, ph, pl, ref)
-    return _LONG[key]
+        _LONG[B] = (sd, ph, pl, ref)
+    return _LONG[B]
 
 
 @pytest.mark.parametrize("B", [1, 32])
-def test_inference_1000_frames_never_stop_drift(B):
+def test_inference_1000_frames_free_running_drift(B):
     sd, ph, pl, ref = _long_case(B)
     out = _model(sd).inference(ph, pl, max_len=1001)
     torch.cuda.synchronize()
-    assert out["pred_melspec"].shape == (B, 1000, 80)
+    assert out["pred_melspec"].shape == (B, 1000, 80) and out["pred_stop"].shape == (B, 1000, 1)
     g, r = out["pred_melspec"].float().cpu(), ref["pred_melspec"]
     gp, rp = out["post_melspec"].float().cpu(), ref["post_melspec"]
     for s in range(0, 1000, 100):
         e = (g[:, s:s + 100] - r[:, s:s + 100])
         ep = (gp[:, s:s + 100] - rp[:, s:s + 100])
-        print(f"AR B{B} frames {s:4d}-{s + 99:4d}: pred max_abs={float(e.abs().max()):.4f} "
+        print(f"AR free-running B{B} frames {s:4d}-{s + 99:4d}: pred max_abs={float(e.abs().max()):.4f} "
               f"rel_l2={float(e.norm() / r[:, s:s + 100].norm()):.4f} | post max_abs={float(ep.abs().max()):.4f} "
               f"rel_l2={float(ep.norm() / rp[:, s:s + 100].norm()):.4f} | stop max_abs="
               f"{float((out['pred_stop'].cpu()[:, s:s + 100] - ref['pred_stop'][:, s:s + 100]).abs().max()):.4f}")
-    _cmp(out, ref, f"AR-1000 never-stop B{B}")
+    assert torch.isfinite(out["post_melspec"]).all()
+    n = FREE_GATE_FRAMES[B]
+    # PostNet has a 5x5-tap receptive field of +-10 frames: compare post over the gated prefix minus that halo
+    head = {"pred_melspec": out["pred_melspec"][:, :n], "post_melspec": out["post_melspec"][:, :n - 10],
+            "pred_stop": out["pred_stop"][:, :n]}
+    href = {"pred_melspec": ref["pred_melspec"][:, :n], "post_melspec": ref["post_melspec"][:, :n - 10],
+            "pred_stop": ref["pred_stop"][:, :n]}
+    _cmp(head, href, f"AR-1000 free-running B{B}, first {n} frames")
 
 
-@pytest.mark.parametrize("B", [1, 32])
-def test_inference_1000_frame_horizon_planted_stop_index(B):
-    """Identical stop-frame index (model/model.py:382-384) late in the 1000-frame horizon, margin >= 0.25 on both sides."""
-    sd, ph, pl, ref = _long_case(B, replicate=B > 1)
-    z = ref["pred_stop"][..., 0] + 1.0e4
-    bias, n_frames, margin = O.plant_from_logits(z, min_t=LONG_MIN_T, delta=0.25)
+@pytest.mark.parametrize("B,seed,min_t", [(1, 317, 250)])
+def test_inference_free_running_planted_stop_late(B, seed, min_t):
+    """Identical stop-frame index (model/model.py:382-384) for a free-running decode as late as the chaos allows."""
+    sd = O.make_state_dict(seed, stop_bias=-1e4)
+    ph, _, pl, _ = O.make_inputs(B, 150, 8, seed=seed + 1)
+    ref = O.inference_cached(sd, ph, pl, max_len=401)
+    bias, n_frames, margin = O.plant_from_logits(ref["pred_stop"][..., 0] + 1.0e4, min_t=min_t, delta=0.25)
     sd2 = dict(sd)
     sd2["linear2.linear.bias"] = torch.tensor([bias])
-    out = _model(sd2).inference(ph, pl, max_len=1001)
+    out = _model(sd2).inference(ph, pl, max_len=401)
     torch.cuda.synchronize()
-    print(f"AR-1000 planted B{B}: frames got={out['pred_melspec'].shape[1]} ref={n_frames} margin={margin:.3f}")
-    assert n_frames >= LONG_MIN_T and margin >= 0.25
-    assert out["pred_melspec"].shape[1] == n_frames                       # identical stop-frame index
+    print(f"AR free-running planted B{B}: frames got={out['pred_melspec'].shape[1]} ref={n_frames} margin={margin:.3f}")
+    assert n_frames >= min_t and out["pred_melspec"].shape[1] == n_frames
     pred = ref["pred_melspec"][:, :n_frames]
     cut = {"pred_melspec": pred, "post_melspec": O.postnet(sd, pred) + pred,
            "pred_stop": ref["pred_stop"][:, :n_frames] + 1.0e4 + bias}
-    _cmp(out, cut, f"AR-1000 planted B{B}")
+    _cmp(out, cut, f"AR free-running planted B{B}")
+
+
+@pytest.mark.parametrize("B", [1, 32])
+def test_inference_1000_frames_teacher_forced_parity_and_stop_index(B):
+    """All 1000 steps through the decode kernel and its K/V cache on the oracle's trajectory: one-step-ahead parity of
+    every frame and stop logit, and the identical stop index for a stop planted at frame 859 (B=32: the B=1 utterance in
+    every row -- 32 independent rows have no late all-rows crossing -- through the batch-32 plan and its cross-cluster
+    stop counting)."""
+    sd, ph, pl, ref = _long_case(B)          # B=32: the ragged batch (encoder unmasked over the padding, SURVEY F8)
+    m = _model(sd)
+    out = m.inference(ph, pl, max_len=1001, forced_melspec=ref["pred_melspec"])
+    torch.cuda.synchronize()
+    assert out["pred_melspec"].shape == (B, 1000, 80)
+    e = (out["pred_melspec"].float().cpu() - ref["pred_melspec"]).abs()
+    es = (out["pred_stop"].float().cpu() - ref["pred_stop"]).abs()
+    for s in range(0, 1000, 100):
+        print(f"AR teacher-forced B{B} frames {s:4d}-{s + 99:4d}: pred max_abs={float(e[:, s:s + 100].max()):.4f} "
+              f"stop max_abs={float(es[:, s:s + 100].max()):.4f}")
+    assert float(e.max()) <= FORCED_PRE_ATOL and float(es.max()) <= FORCED_STOP_ATOL, (float(e.max()), float(es.max()))
+    ok, msg = report(f"AR teacher-forced B{B} post", out["post_melspec"], ref["post_melspec"], FORCED_POST_ATOL)
+    print(msg)
+    assert ok, msg
+    # planted stop late in the horizon
+    sd, ph, pl, ref = _long_case(1)
+    if B > 1:
+        ph, pl = ph.repeat(B, 1), pl.repeat(B)
+        ref = {k: v.repeat(B, 1, 1) for k, v in ref.items()}
+    bias, n_frames, margin = O.plant_from_logits(ref["pred_stop"][..., 0] + 1.0e4, min_t=LONG_MIN_T, delta=0.25)
+    sd2 = dict(sd)
+    sd2["linear2.linear.bias"] = torch.tensor([bias])
+    out2 = _model(sd2).inference(ph, pl, max_len=1001, forced_melspec=ref["pred_melspec"])
+    torch.cuda.synchronize()
+    print(f"AR teacher-forced planted B{B}: frames got={out2['pred_melspec'].shape[1]} ref={n_frames} margin={margin:.3f}")
+    assert n_frames >= LONG_MIN_T and margin >= 0.25
+    assert out2["pred_melspec"].shape[1] == n_frames                      # identical stop-frame index
+    assert float((out2["pred_melspec"].cpu() - ref["pred_melspec"][:, :n_frames]).abs().max()) <= FORCED_PRE_ATOL
+    if B > 1:       # identical rows stay bit-identical across the clusters that own them
+        assert torch.equal(out2["pred_melspec"][0], out2["pred_melspec"][B - 1])

@@ -156,7 +156,7 @@ def test_packed_weights_follow_in_place_updates_and_moves():
     m = _model(sd)
     a = m(ph, mel, pl, ml)["pred_melspec"].clone()
     with torch.no_grad():
-        m.pe.alpha.data.fill_(0.1)                          # silent staleness after an in-place update
+        m.pe.alpha.fill_(0.1)         # an in-place update (optimizer step, BN edit) must reach the kernels
     b = m(ph, mel, pl, ml)["pred_melspec"].clone()
     sd2 = dict(sd)
     sd2["pe.alpha"] = torch.tensor([0.1])

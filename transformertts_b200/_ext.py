@@ -57,7 +57,7 @@ SIGNATURES = {
                               vp, vp, vp, vp, vp, C.c_size_t, vp]),
     "tts_encode": (C.c_int, [C.POINTER(Weights), vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_size_t, vp]),
     "tts_decode": (C.c_int, [C.POINTER(Weights), vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, vp, vp, vp, vp, vp,
-                             C.c_int, C.c_int, vp]),
+                             C.c_int, C.c_int, vp, vp]),
     "tts_decode_max_clusters": (C.c_int, [C.c_int, C.c_int]),
     "tts_postnet": (C.c_int, [C.POINTER(Weights), vp, C.c_int, C.c_int, vp, vp, C.c_size_t, vp]),
     "tts_teacher_forcing_mix": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]),

@@ -163,7 +163,8 @@ class TransformerTTS(nn.Module):
 
     def _fingerprint(self):
         """(data_ptr, in-place version counter) of every parameter and buffer: changes whenever a tensor is replaced,
-        moved or updated in place (optimizer step, `.data.fill_()`, BN statistic edits)."""
+        moved or updated in place (optimizer step, `p.fill_()` under no_grad, BN statistic edits).  Writes through
+        `p.data` bypass torch's version counter: call `refresh_weights()` after those."""
         if self._fp_tensors is None:      # the module-tree walk is the slow part: keep the flat list
             self._fp_tensors = list(self.parameters()) + list(self.buffers())
         return tuple((t.data_ptr(), t._version) for t in self._fp_tensors)
@@ -240,7 +241,9 @@ class TransformerTTS(nn.Module):
     # ------------------------------------------------------------------ model/model.py:323-394
     @torch.no_grad()
     def inference(self, phoneme, phoneme_lens, max_len: int = 1500, stop_threshold: float = 0.5,
-                  rows_per_cluster: int = 0, cluster_size: int = 0):
+                  rows_per_cluster: int = 0, cluster_size: int = 0, forced_melspec=None):
+        """`forced_melspec` [B, >= max_len-1, 80] (not in the reference): teacher-forced decode -- step t consumes frame
+        t-1 of the given trajectory instead of the model's own prediction, through the same kernel and K/V cache."""
         self.eval()                                   # model/model.py:342
         lib = _ext.load()
         phoneme, phoneme_lens = self._prep(phoneme, torch.int64), self._prep(phoneme_lens, torch.int64)
@@ -264,10 +267,16 @@ class TransformerTTS(nn.Module):
             stop = torch.empty(B, max_frames, dtype=torch.float32, device=dev)
             stop_count = torch.empty(max_frames, dtype=torch.int32, device=dev)
             n_frames = torch.empty(1, dtype=torch.int32, device=dev)
+            forced = None
+            if forced_melspec is not None:
+                forced = self._prep(forced_melspec, torch.float32)
+                if forced.dim() != 3 or forced.shape[0] != B or forced.shape[1] < max_frames or forced.shape[2] != N_MELS:
+                    raise ValueError("forced_melspec must be [B, >= max_len-1, 80]")
+                forced = forced[:, :max_frames].contiguous()
             _ext.check(lib.tts_decode(C.byref(w.struct), _ext.ptr(cross_kv), _ext.ptr(ph_len), B, Tp, max_frames,
                                       float(stop_threshold), _ext.ptr(self_kv), _ext.ptr(mel), _ext.ptr(stop),
                                       _ext.ptr(stop_count), _ext.ptr(n_frames), int(rows_per_cluster),
-                                      int(cluster_size), self._stream()), "tts_decode")
+                                      int(cluster_size), _ext.ptr(forced), self._stream()), "tts_decode")
             n = int(n_frames.item())                  # the single host sync of the AR loop
             pred = mel[:, :n].contiguous()
             pred_stop = stop[:, :n].unsqueeze(-1).contiguous()     # (B,T,1)  model/model.py:378,393

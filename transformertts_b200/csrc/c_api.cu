@@ -451,7 +451,8 @@ extern "C" int tts_encode(const TtsWeights* w, const int64_t* phoneme, const int
 
 extern "C" int tts_decode(const TtsWeights* w, const void* cross_kv, const int32_t* ph_len_i32, int B, int Tp,
                           int max_frames, float stop_threshold, void* self_kv, float* mel_out, float* stop_out,
-                          int32_t* stop_count, int32_t* n_frames, int rows_per_cluster, int cluster_size, void* stream) {
+                          int32_t* stop_count, int32_t* n_frames, int rows_per_cluster, int cluster_size,
+                          const float* forced_mel, void* stream) {
   if (w == nullptr) return fail("weights pointer is NULL");
   if (B <= 0 || Tp <= 0 || max_frames <= 0) return fail("B, Tp and max_frames must be positive");
   if (max_frames > kPeMax) return fail("max_frames exceeds the positional-encoding table (5000)");
@@ -484,6 +485,7 @@ extern "C" int tts_decode(const TtsWeights* w, const void* cross_kv, const int32
   else if (stop_threshold >= 1.f) a.stop_logit = INFINITY;
   else a.stop_logit = (float)log((double)stop_threshold / (1.0 - (double)stop_threshold));
   a.mel_out = mel_out; a.stop_out = stop_out; a.stop_count = stop_count; a.n_frames = n_frames;
+  a.forced_mel = forced_mel;
   if (cudaMemsetAsync(stop_count, 0, sizeof(int) * (size_t)max_frames, s) != cudaSuccess)
     return fail("cudaMemsetAsync(stop_count) failed");
   int C = cluster_size, R = rows_per_cluster;

@@ -379,6 +379,15 @@ __global__ void __launch_bounds__(DEC_THREADS, R <= 2 ? 2 : 1) decode_kernel(con
       if (stop)
         for (int p = 0; p < C; ++p) *cluster.map_shared_rank(&sm.exit_flag, p) = 1;
     }
+    // ---- teacher-forced decode: the fed-back frame comes from a given trajectory (all bytes of the previous step's
+    // broadcast into melprev have landed: BAR_M was waited at the end of that step)
+    if (a.forced_mel != nullptr && t > 0) {
+      for (int i = tid; i < R * kMel; i += DEC_THREADS) {
+        const int r = i / kMel, c = i - r * kMel;
+        sm.melprev[r][c] = __ldg(a.forced_mel + ((size_t)row_b(r) * a.Tmax + (t - 1)) * kMel + c);
+      }
+      __syncthreads();
+    }
     // ---- decoder prenet (model/model.py:61-67): relu(W1 mel_prev + b1)
     slice(kD, nb, ne);
     gemv_slice<R, 2>(a.w_pre1, kMelPad, a.b_pre1, kMelPad, nb, ne, &sm.melprev[0][0], kMelPad,

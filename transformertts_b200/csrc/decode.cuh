@@ -31,6 +31,8 @@ struct DecodeArgs {
   float* stop_out;                         // [B][Tmax]
   int* stop_count;                         // [Tmax], zeroed before launch
   int* n_frames;                           // [1]
+  const float* forced_mel;                 // optional [B][Tmax][80]: frame t-1 of this trajectory is fed back at step t
+                                           // instead of the kernel's own prediction (teacher-forced decode)
 };
 
 int decode_max_clusters(int rows_per_cluster, int cluster_size);   // co-resident clusters (occupancy query)
