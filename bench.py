@@ -560,7 +560,7 @@ def run_ours(args):
                                              "decode steps + PostNet, pred / post / stop copied to pinned host memory"}}
 
     # ---- batch-sharded AR decode (configs[3]): 512 utterances dealt in contiguous blocks to the ranks
-    # (sharding.shard_bounds), micro-batches of 32 / 64 (each one inference() call), 1000 frames each, no collective
+    # (sharding.shard_bounds), micro-batches of 32 / 64 / 128 (each one inference() call), 1000 frames each, no collective
     ar_sharded = None
     if not args.no_ar and not args.no_extra:
         from transformertts_b200.sharding import shard_bounds, micro_batches
@@ -569,7 +569,7 @@ def run_ours(args):
         lo, hi = shard_bounds(NU, world, rank)
         uph, upl = uph.to(dev), upl.to(dev)
         ar_sharded = {"utterances": NU, "frames_each": 1000, "per_rank": hi - lo, "scaling": "strong"}
-        for mb in (32, 64):
+        for mb in (32, 64, 128):
             parts = micro_batches(lo, hi, mb)
 
             def run_block():

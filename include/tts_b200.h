@@ -78,6 +78,12 @@ typedef struct TtsWeights {
    * layer l, 512 l + [256,512) = Wv of layer l (copies of dec[l].ca.w_in rows 256-767), f32 [1536] likewise.  Lets
    * tts_forward project the memory once for all layers.  May be NULL: the per-layer matrices are used then. */
   const void* ckv_w; const float* ckv_b;
+  /* K-blocked transposes for the AR decode kernel's K-split projections: bf16 [K/8][256][8], element [kb][n][i] =
+   * W[n][8 kb + i], so that 256 threads (one per output n) read consecutive 16-byte words of a K slice.
+   * dec_kt[l][0] = dec[l].sa.w_out (K = 256), [l][1] = dec[l].ca.w_out (K = 256), [l][2] = dec[l].ffn.w2 (K = 1024);
+   * pre2_kt = pre2_w (K = 256).  Required by tts_decode. */
+  const void* dec_kt[3][3];
+  const void* pre2_kt;
 } TtsWeights;
 
 int tts_abi_version(void);
@@ -118,6 +124,11 @@ int tts_decode(const TtsWeights* w, const void* cross_kv, const int32_t* ph_len_
 /* Number of thread-block clusters of the decode kernel the current device holds at once for a given plan
  * (cudaOccupancyMaxActiveClusters); 0 if the plan cannot run. */
 int tts_decode_max_clusters(int rows_per_cluster, int cluster_size);
+
+/* Utterances one tts_decode launch holds co-resident on the current device (largest one-wave plan).  A larger batch is
+ * still decoded correctly, in waves, but then the stop rule cannot end the launch early: callers should split larger
+ * batches into micro-batches of at most this many rows (transformertts_b200.sharding does). */
+int tts_decode_capacity(void);
 
 /* PostNet with residual: mel_post = PostNet(mel_pre) + mel_pre, f32 [B][T][80] both. */
 int tts_postnet(const TtsWeights* w, const float* mel_pre, int B, int T, float* mel_post, void* workspace,

@@ -44,6 +44,7 @@ class Weights(C.Structure):
         ("post_w", vp * 5), ("post_b", fp * 5),
         ("pe", fp), ("alpha", f32), ("reserved1", i32),
         ("ckv_w", vp), ("ckv_b", fp),
+        ("dec_kt", (vp * 3) * 3), ("pre2_kt", vp),
     ]
 
 
@@ -59,6 +60,7 @@ SIGNATURES = {
     "tts_decode": (C.c_int, [C.POINTER(Weights), vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, vp, vp, vp, vp, vp,
                              C.c_int, C.c_int, vp, vp]),
     "tts_decode_max_clusters": (C.c_int, [C.c_int, C.c_int]),
+    "tts_decode_capacity": (C.c_int, []),
     "tts_postnet": (C.c_int, [C.POINTER(Weights), vp, C.c_int, C.c_int, vp, vp, C.c_size_t, vp]),
     "tts_teacher_forcing_mix": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]),
     "tts_loss_scratch_bytes": (C.c_size_t, []),

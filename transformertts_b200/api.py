@@ -133,6 +133,8 @@ class TransformerTTS(nn.Module):
         self._packed: Optional[PackedWeights] = None
         self._packed_fp = None
         self._fp_tensors = None
+        self._decode_capacity = None
+        self._warned_capacity = False
         self._ws = None
         self.register_load_state_dict_post_hook(lambda module, incompatible: module.refresh_weights())
 
@@ -255,6 +257,14 @@ class TransformerTTS(nn.Module):
             raise ValueError("max_len must be >= 2 (the reference produces at most max_len-1 frames)")
         dev = self.device
         with torch.cuda.device(dev):
+            if self._decode_capacity is None:
+                self._decode_capacity = int(lib.tts_decode_capacity())
+            if B > self._decode_capacity and not self._warned_capacity:
+                import warnings
+                warnings.warn(f"inference(): batch {B} exceeds the {self._decode_capacity} utterances one decode launch holds "
+                              "co-resident; the result is still exact but the launch cannot stop early. Split the batch "
+                              "(transformertts_b200.sharding.micro_batches).")
+                self._warned_capacity = True
             w = self._weights()
             ws, ws_bytes = self._workspace(B, Tp, 1)
             cross_kv = torch.empty(3 * B * Tp * 512, dtype=torch.bfloat16, device=dev)

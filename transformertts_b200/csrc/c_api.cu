@@ -157,6 +157,7 @@ extern "C" const char* tts_last_error(void) { return g_err; }
 extern "C" int tts_decode_max_clusters(int rows_per_cluster, int cluster_size) {
   return decode_max_clusters(rows_per_cluster, cluster_size);
 }
+extern "C" int tts_decode_capacity(void) { return decode_capacity(); }
 extern "C" uint64_t tts_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 extern "C" size_t tts_workspace_bytes(int B, int Tp, int Tm) {
   if (B <= 0 || Tp <= 0 || Tm < 0) return 0;
@@ -456,6 +457,10 @@ extern "C" int tts_decode(const TtsWeights* w, const void* cross_kv, const int32
   if (w == nullptr) return fail("weights pointer is NULL");
   if (B <= 0 || Tp <= 0 || max_frames <= 0) return fail("B, Tp and max_frames must be positive");
   if (max_frames > kPeMax) return fail("max_frames exceeds the positional-encoding table (5000)");
+  if (w->pre2_kt == nullptr) return fail("tts_decode needs the K-blocked transposes (TtsWeights.dec_kt / pre2_kt)");
+  for (int l = 0; l < 3; ++l)
+    for (int j = 0; j < 3; ++j)
+      if (w->dec_kt[l][j] == nullptr) return fail("tts_decode needs the K-blocked transposes (TtsWeights.dec_kt / pre2_kt)");
   cudaStream_t s = (cudaStream_t)stream;
   DecodeArgs a;
   memset(&a, 0, sizeof(a));
@@ -463,17 +468,17 @@ extern "C" int tts_decode(const TtsWeights* w, const void* cross_kv, const int32
     const TtsDecLayerW& L = w->dec[l];
     DecLayerW& d = a.layer[l];
     d.w_qkv = (const bf16*)L.sa.w_in; d.b_qkv = L.sa.b_in;
-    d.w_so = (const bf16*)L.sa.w_out; d.b_so = L.sa.b_out;
+    d.w_so = (const bf16*)w->dec_kt[l][0]; d.b_so = L.sa.b_out;
     d.ln1_g = L.ln1.g; d.ln1_b = L.ln1.b;
     d.w_cq = (const bf16*)L.ca.w_in; d.b_cq = L.ca.b_in;
-    d.w_co = (const bf16*)L.ca.w_out; d.b_co = L.ca.b_out;
+    d.w_co = (const bf16*)w->dec_kt[l][1]; d.b_co = L.ca.b_out;
     d.ln2_g = L.ln2.g; d.ln2_b = L.ln2.b;
     d.w_f1 = (const bf16*)L.ffn.w1; d.b_f1 = L.ffn.b1;
-    d.w_f2 = (const bf16*)L.ffn.w2; d.b_f2 = L.ffn.b2;
+    d.w_f2 = (const bf16*)w->dec_kt[l][2]; d.b_f2 = L.ffn.b2;
     d.ln3_g = L.ln3.g; d.ln3_b = L.ln3.b;
   }
   a.w_pre1 = (const bf16*)w->pre1_w; a.b_pre1 = w->pre1_b;
-  a.w_pre2 = (const bf16*)w->pre2_w; a.b_pre2 = w->pre2_b;
+  a.w_pre2 = (const bf16*)w->pre2_kt; a.b_pre2 = w->pre2_b;
   a.w_head = (const bf16*)w->head_w; a.b_head = w->head_b;
   a.pe = w->pe; a.alpha = w->alpha;
   a.cross_kv = (const bf16*)cross_kv;
@@ -491,8 +496,9 @@ extern "C" int tts_decode(const TtsWeights* w, const void* cross_kv, const int32
   int C = cluster_size, R = rows_per_cluster;
   if (C <= 0 && R <= 0) {
     decode_plan(B, &R, &C);
-  } else if (C <= 0) {
+  } else if (C <= 0) {                               // largest cluster whose landing buffers fit and that runs in one wave
     C = 16;
+    while (C > 4 && (B + R - 1) / R > decode_max_clusters(R, C)) C >>= 1;
   } else if (R <= 0) {                               // fewest rows per cluster that still fits one wave
     R = 1;
     while (R < 8 && (B + R - 1) / R > decode_max_clusters(R, C)) R *= 2;

@@ -8,6 +8,8 @@ Host-side preparation done once per checkpoint:
     (torch/nn/functional.py:6632 scales q before q k^T)
   * mel (80x256) and stop (1x256) heads stacked into one [81][256] matrix
   * matrices cast to bf16, biases / LayerNorm / PE table kept fp32
+  * K-blocked transposes [K/8][256][8] of the decoder out-projections, FFN second matrices and prenet second matrix
+    for the AR decode kernel's K-split contractions
 """
 from __future__ import annotations
 
@@ -114,6 +116,16 @@ class PackedWeights:
         # cross-attention K/V projections of all decoder layers stacked (rows 256-767 of each in_proj): one GEMM
         s.ckv_w = mat(torch.cat([sd[f"decoder.layers.{l}.multihead_attn.in_proj_weight"][D:].float() for l in range(3)]))
         s.ckv_b = vec(torch.cat([sd[f"decoder.layers.{l}.multihead_attn.in_proj_bias"][D:].float() for l in range(3)]))
+        # K-blocked transposes [K/8][256][8] of the matrices the AR decode kernel contracts K-split (decode.cu)
+        def kt(w):
+            n, k = w.shape
+            return mat(w.float().view(n, k // 8, 8).permute(1, 0, 2))
+        for l in range(3):
+            p = f"decoder.layers.{l}"
+            s.dec_kt[l][0] = kt(sd[f"{p}.self_attn.out_proj.weight"])
+            s.dec_kt[l][1] = kt(sd[f"{p}.multihead_attn.out_proj.weight"])
+            s.dec_kt[l][2] = kt(sd[f"{p}.linear2.weight"])
+        s.pre2_kt = kt(sd["dec_prenet.linear2.linear.weight"])
         s.pe = vec(sd["pe.pe"])
         s.alpha = float(sd["pe.alpha"].reshape(-1)[0])
         self.struct = s
