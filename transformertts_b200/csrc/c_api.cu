@@ -328,26 +328,92 @@ static int check_common(const TtsWeights* w, int B, int Tp, int Tm, const void* 
 }
 
 // ------------------------------------------------------------------ side stream for the encoder branch
-// The encoder (+ the per-layer cross K/V projections of its output) and the decoder front (prenet, layer-0
-// self-attention block) are independent until the first cross-attention; tts_forward runs the encoder branch on a
-// per-device side stream, forked from and joined back into the caller's stream with events, so its many small
-// launches fill the tails and launch gaps of the decoder kernels.
+// The encoder (+ the cross K/V projections of its output) and the decoder front (prenet, layer-0 self-attention
+// block) are independent until the first cross-attention; tts_forward runs the encoder branch on a per-device side
+// stream, forked from and joined back into the caller's stream with events, so its many small launches fill the tails
+// and launch gaps of the decoder kernels.
+// Measured and NOT kept (profiles/r02_fwd_split_ab.txt): the decoder stack as 2 / 3 / 4 independent sub-batches on their
+// own streams (utterances are independent), hoping that the SMs one chain's kernel frees while it drains run the other
+// chain's kernel: 1.13 -> 1.21 / 1.37 / 1.40 ms per cfg-2 forward -- every kernel is persistent with one CTA per SM, so
+// two chains only take SMs away from each other.
 #include <mutex>
-struct SideStream { cudaStream_t stream; cudaEvent_t fork, join; bool ok; };
+struct SideStream { cudaStream_t enc; cudaEvent_t fork, enc_join; bool ok; };
 static SideStream* side_stream() {
-  static SideStream table[64] = {};
+  static SideStream table[kMaxDevices] = {};
   static std::mutex mu;
   int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
   std::lock_guard<std::mutex> lock(mu);
   SideStream& s = table[dev];
   if (!s.ok) {
-    if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaStreamCreateWithFlags(&s.enc, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     if (cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-    if (cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&s.enc_join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
     s.ok = true;
   }
   return &s;
+}
+
+// Decoder stack + heads + PostNet for utterances [b0, b0 + nb) of the batch on stream s (model/model.py:297-313).
+// `enc_join` (nullable): event after which the encoder branch's memory / cross K/V are complete.
+static const char* run_decoder(const TtsWeights* w, const void* mel, int flags, int B, int Tp, int Tm, int b0, int nb,
+                               float* mel_pre, float* mel_post, float* stop, float* align, Workspace& ws,
+                               cudaEvent_t enc_join, cudaStream_t s) {
+  const size_t r0 = (size_t)b0 * Tm;                 // first decoder row of this part
+  const int Nm = nb * Tm;
+  const char* e;
+  bf16* mel_in = ws.mel_in + r0 * kMel;
+  const bf16* mel16 = mel_in;
+  if (flags & TTS_FLAG_MEL_BF16) {
+    mel16 = reinterpret_cast<const bf16*>(mel) + r0 * kMel;       // read in place by the prenet's TMA loads
+  } else {
+    if ((e = cast_mel_launch(reinterpret_cast<const float*>(mel) + r0 * kMel, mel_in, (size_t)Nm * kMel, s))) return e;
+  }
+  bf16 *d0 = ws.d0 + r0 * kD, *d1 = ws.d1 + r0 * kD, *qkv = ws.qkv_d + r0 * 3 * kD, *att = ws.att_d + r0 * kD;
+  bf16 *cq = ws.cq + r0 * kD, *ffn = ws.ffn_d + r0 * kF, *pre16 = ws.mel_pre16 + r0 * kMel;
+  const int* mel_len = ws.mel_len + b0;
+  const int* ph_len = ws.ph_len + b0;
+  {
+    // decoder prenet on the go-frame-shifted target (model/model.py:278-279, 297): frame t reads mel[t-1]
+    GemmArgs g = conv_args(mel16, nb, Tm, kMel, w->pre1_w, w->pre1_b, kD, 1, -1);
+    g.act = ACT_RELU; g.out_bf16 = d0; g.ld_bf16 = kD;
+    if ((e = gemm_launch(g, s))) return e;
+    GemmArgs h = linear_args(d0, Nm, kD, w->pre2_w, w->pre2_b, kD);
+    h.act = ACT_RELU; h.pe = w->pe; h.alpha = w->alpha; h.pe_period = Tm;
+    h.out_bf16 = d1; h.ld_bf16 = kD;
+    if ((e = gemm_launch(h, s))) return e;
+  }
+  bf16* x = d1; bf16* y = d0;
+  bool joined = enc_join == nullptr;
+  const bool ckv_stacked = w->ckv_w != nullptr && w->ckv_b != nullptr;
+  const size_t Np_all = (size_t)B * Tp;
+  for (int l = 0; l < 3; ++l) {                      // model/layers.py:46-50 (post-norm)
+    const TtsDecLayerW& L = w->dec[l];
+    if ((e = proj(x, Nm, kD, L.sa.w_in, L.sa.b_in, 3 * kD, ACT_NONE, qkv, s))) return e;
+    if ((e = run_attention(qkv, 3 * kD, qkv + kD, qkv + 2 * kD, 3 * kD, att, nullptr, mel_len, nb, Tm, Tm, 1, s))) return e;
+    if ((e = proj_res_ln(att, Nm, kD, L.sa.w_out, L.sa.b_out, x, L.ln1, y, s))) return e;            // y = LN1
+    if ((e = proj(y, Nm, kD, L.ca.w_in, L.ca.b_in, kD, ACT_NONE, cq, s))) return e;
+    if (!joined) {                                   // first use of the encoder branch's results
+      if (cudaStreamWaitEvent(s, enc_join, 0) != cudaSuccess) return "side stream join failed";
+      joined = true;
+    }
+    const bf16* ckv = ckv_stacked ? ws.ckv + (size_t)b0 * Tp * 6 * kD + (size_t)l * 2 * kD
+                                  : ws.ckv + (size_t)l * Np_all * 2 * kD + (size_t)b0 * Tp * 2 * kD;
+    const int ld_ckv = ckv_stacked ? 6 * kD : 2 * kD;
+    float* probs = (flags & TTS_FLAG_WANT_ALIGN) ? align + ((size_t)l * B + b0) * kH * Tm * Tp : nullptr;
+    if ((e = run_attention(cq, kD, ckv, ckv + kD, ld_ckv, att, probs, ph_len, nb, Tm, Tp, 0, s))) return e;
+    if ((e = proj_res_ln(att, Nm, kD, L.ca.w_out, L.ca.b_out, y, L.ln2, x, s))) return e;            // x = LN2
+    if ((e = ffn_block(x, Nm, L.ffn, L.ln3, ffn, y, s))) return e;                                   // y = LN3
+    bf16* t = x; x = y; y = t;
+  }
+  {                                                  // mel + stop heads (model/model.py:309,313)
+    GemmArgs g = linear_args(x, Nm, kD, w->head_w, w->head_b, kMel + 1);
+    g.out_f32 = mel_pre + r0 * kMel; g.ld_f32 = kMel;
+    g.out_bf16 = pre16; g.ld_bf16 = kMel;
+    g.out_last = stop + r0;
+    if ((e = gemm_launch(g, s))) return e;
+  }
+  return run_postnet(w, pre16, mel_pre + r0 * kMel, nb, Tm, qkv, ffn, mel_post + r0 * kMel, s);
 }
 
 // ------------------------------------------------------------------ TransformerTTS.forward
@@ -356,81 +422,35 @@ extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const vo
                            float* stop, float* align, void* workspace, size_t ws_bytes, void* stream) {
   if (check_common(w, B, Tp, Tm, workspace, ws_bytes)) return 1;
   if ((flags & TTS_FLAG_WANT_ALIGN) && align == nullptr) return fail("WANT_ALIGN set but align is NULL");
+  if ((flags & TTS_FLAG_MEL_BF16) && (reinterpret_cast<uintptr_t>(mel) & 15) != 0) return fail("bf16 mel must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   Workspace ws = carve(workspace, B, Tp, Tm);
-  const int Np = B * Tp, Nm = B * Tm;
+  const int Np = B * Tp;
   TRY(lens_launch(ph_lens, ws.ph_len, B, 1, Tp, s));
   TRY(lens_launch(mel_lens, ws.mel_len, B, 1, Tm, s));
   static const bool env_serial = getenv("TTS_SERIAL") != nullptr;
   SideStream* side = (env_serial || (flags & TTS_FLAG_SERIAL)) ? nullptr : side_stream();
   cudaStream_t se = s;                               // stream of the encoder branch
   if (side != nullptr) {
-    if (cudaEventRecord(side->fork, s) != cudaSuccess || cudaStreamWaitEvent(side->stream, side->fork, 0) != cudaSuccess)
+    if (cudaEventRecord(side->fork, s) != cudaSuccess || cudaStreamWaitEvent(side->enc, side->fork, 0) != cudaSuccess)
       return fail("side stream fork failed");
-    se = side->stream;
+    se = side->enc;
   }
-  const char* enc_err = run_encoder(w, phoneme, B, Tp, (flags & TTS_FLAG_ENC_MASK) != 0, ws, se);
+  const char* err = run_encoder(w, phoneme, B, Tp, (flags & TTS_FLAG_ENC_MASK) != 0, ws, se);
   const bf16* memory = ws.e0;
-  const bool ckv_stacked = w->ckv_w != nullptr && w->ckv_b != nullptr;   // one [Np][1536] projection for all layers
-  if (ckv_stacked) {
-    if (enc_err == nullptr) enc_err = proj(memory, Np, kD, w->ckv_w, w->ckv_b, 6 * kD, ACT_NONE, ws.ckv, se);
+  if (w->ckv_w != nullptr && w->ckv_b != nullptr) {  // one [Np][1536] projection for all layers
+    if (err == nullptr) err = proj(memory, Np, kD, w->ckv_w, w->ckv_b, 6 * kD, ACT_NONE, ws.ckv, se);
   } else {
-    for (int l = 0; l < 3 && enc_err == nullptr; ++l)
-      enc_err = run_cross_kv(w, l, memory, Np, ws.ckv + (size_t)l * Np * 2 * kD, se);
+    for (int l = 0; l < 3 && err == nullptr; ++l)
+      err = run_cross_kv(w, l, memory, Np, ws.ckv + (size_t)l * Np * 2 * kD, se);
   }
-  if (side != nullptr && cudaEventRecord(side->join, se) != cudaSuccess) return fail("side stream join failed");
-  struct JoinGuard {                                 // whatever path leaves this function, the caller's stream
-    SideStream* side; cudaStream_t s; bool joined;   // ends up ordered after the encoder branch
-    ~JoinGuard() { if (!joined) cudaStreamWaitEvent(s, side->join, 0); }
-  } guard{side, s, side == nullptr};
-  bool& joined = guard.joined;
-  if (enc_err != nullptr) return fail(enc_err);
-
-  // decoder prenet on the go-frame-shifted target (model/model.py:278-279, 297): frame t reads mel[t-1]
-  const bf16* mel16 = ws.mel_in;
-  if (flags & TTS_FLAG_MEL_BF16) {
-    if ((reinterpret_cast<uintptr_t>(mel) & 15) != 0) return fail("bf16 mel must be 16-byte aligned");
-    mel16 = reinterpret_cast<const bf16*>(mel);      // read in place by the prenet's TMA loads
-  } else {
-    TRY(cast_mel_launch(reinterpret_cast<const float*>(mel), ws.mel_in, (size_t)Nm * kMel, s));
-  }
-  {
-    GemmArgs g = conv_args(mel16, B, Tm, kMel, w->pre1_w, w->pre1_b, kD, 1, -1);
-    g.act = ACT_RELU; g.out_bf16 = ws.d0; g.ld_bf16 = kD;
-    TRY(gemm_launch(g, s));
-    GemmArgs h = linear_args(ws.d0, Nm, kD, w->pre2_w, w->pre2_b, kD);
-    h.act = ACT_RELU; h.pe = w->pe; h.alpha = w->alpha; h.pe_period = Tm;
-    h.out_bf16 = ws.d1; h.ld_bf16 = kD;
-    TRY(gemm_launch(h, s));
-  }
-  bf16* x = ws.d1; bf16* y = ws.d0;
-  for (int l = 0; l < 3; ++l) {                      // model/layers.py:46-50 (post-norm)
-    const TtsDecLayerW& L = w->dec[l];
-    TRY(proj(x, Nm, kD, L.sa.w_in, L.sa.b_in, 3 * kD, ACT_NONE, ws.qkv_d, s));
-    TRY(run_attention(ws.qkv_d, 3 * kD, ws.qkv_d + kD, ws.qkv_d + 2 * kD, 3 * kD, ws.att_d, nullptr, ws.mel_len, B, Tm,
-                      Tm, 1, s));
-    TRY(proj_res_ln(ws.att_d, Nm, kD, L.sa.w_out, L.sa.b_out, x, L.ln1, y, s));            // y = LN1
-    TRY(proj(y, Nm, kD, L.ca.w_in, L.ca.b_in, kD, ACT_NONE, ws.cq, s));
-    if (!joined) {                                   // first use of the encoder branch's results
-      if (cudaStreamWaitEvent(s, side->join, 0) != cudaSuccess) return fail("side stream join failed");
-      joined = true;
-    }
-    const bf16* ckv = ckv_stacked ? ws.ckv + (size_t)l * 2 * kD : ws.ckv + (size_t)l * Np * 2 * kD;
-    const int ld_ckv = ckv_stacked ? 6 * kD : 2 * kD;
-    float* probs = (flags & TTS_FLAG_WANT_ALIGN) ? align + (size_t)l * B * kH * Tm * Tp : nullptr;
-    TRY(run_attention(ws.cq, kD, ckv, ckv + kD, ld_ckv, ws.att_d, probs, ws.ph_len, B, Tm, Tp, 0, s));
-    TRY(proj_res_ln(ws.att_d, Nm, kD, L.ca.w_out, L.ca.b_out, y, L.ln2, x, s));            // x = LN2
-    TRY(ffn_block(x, Nm, L.ffn, L.ln3, ws.ffn_d, y, s));                                   // y = LN3
-    bf16* t = x; x = y; y = t;
-  }
-  {                                                  // mel + stop heads (model/model.py:309,313)
-    GemmArgs g = linear_args(x, Nm, kD, w->head_w, w->head_b, kMel + 1);
-    g.out_f32 = mel_pre; g.ld_f32 = kMel;
-    g.out_bf16 = ws.mel_pre16; g.ld_bf16 = kMel;
-    g.out_last = stop;
-    TRY(gemm_launch(g, s));
-  }
-  TRY(run_postnet(w, ws.mel_pre16, mel_pre, B, Tm, ws.qkv_d, ws.ffn_d, mel_post, s));
+  if (side != nullptr && cudaEventRecord(side->enc_join, se) != cudaSuccess && err == nullptr) err = "side stream join failed";
+  if (err == nullptr)
+    err = run_decoder(w, mel, flags, B, Tp, Tm, 0, B, mel_pre, mel_post, stop, align, ws,
+                      side != nullptr ? side->enc_join : nullptr, s);
+  // whatever path was taken, the caller's stream ends up ordered after the encoder branch
+  if (side != nullptr) cudaStreamWaitEvent(s, side->enc_join, 0);
+  if (err != nullptr) return fail(err);
   return 0;
 }
 

@@ -61,12 +61,15 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // Bounded wait: a protocol bug must surface as a trapped kernel (an error the host reports),
 // never as a hung GPU box.  The bound is wall time (~2 s of SM clock), because one try_wait probe may itself
 // suspend the thread for a hardware-chosen interval.
+#ifndef TTS_WAIT_BOUND_CYCLES
+#define TTS_WAIT_BOUND_CYCLES 4000000000LL   // tools/sanitize.sh builds with a larger bound: compute-sanitizer slows kernels 100x
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
 #pragma unroll 1
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) __trap();
+    if (clock64() - t0 > TTS_WAIT_BOUND_CYCLES) __trap();
   }
 }
 
