@@ -230,9 +230,11 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
         }
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four chains: ILP, only 2 warps per scheduler
 #pragma unroll
-        for (int e = 0; e < 64; e += 4) {
-          mx[0] = fmaxf(mx[0], __uint_as_float(r[e])); mx[1] = fmaxf(mx[1], __uint_as_float(r[e + 1]));
-          mx[2] = fmaxf(mx[2], __uint_as_float(r[e + 2])); mx[3] = fmaxf(mx[3], __uint_as_float(r[e + 3]));
+        for (int e = 0; e < 64; e += 8) {                             // FMNMX3: two scores per instruction
+          mx[0] = fmax3(mx[0], __uint_as_float(r[e]), __uint_as_float(r[e + 1]));
+          mx[1] = fmax3(mx[1], __uint_as_float(r[e + 2]), __uint_as_float(r[e + 3]));
+          mx[2] = fmax3(mx[2], __uint_as_float(r[e + 4]), __uint_as_float(r[e + 5]));
+          mx[3] = fmax3(mx[3], __uint_as_float(r[e + 6]), __uint_as_float(r[e + 7]));
         }
         const float smax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
         m_run = fmaxf(m_run, smax * kLog2e);
@@ -245,13 +247,14 @@ attn2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CU
           grew = true;
         }
         const float nmref = m_used == -INFINITY ? 0.f : -m_used;
-        float sm[4] = {0.f, 0.f, 0.f, 0.f};
+        float sm[4] = {0.f, 0.f, 0.f, 0.f};                          // two FADD2 chains
         uint32_t pk[32];
 #pragma unroll
         for (int e = 0; e < 32; ++e) {
-          const float p0 = fast_exp2(fmaf(__uint_as_float(r[2 * e]), kLog2e, nmref));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(r[2 * e + 1]), kLog2e, nmref));
-          sm[e & 3] += p0 + p1;
+          float x0, x1;                                               // FFMA2: both exponents in one issue slot
+          ffma2(x0, x1, __uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1]), kLog2e, kLog2e, nmref, nmref);
+          const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+          fadd2(sm[2 * (e & 1)], sm[2 * (e & 1) + 1], sm[2 * (e & 1)], sm[2 * (e & 1) + 1], p0, p1);
           pk[e] = pack_bf16(p0, p1);
         }
         l += (sm[0] + sm[1]) + (sm[2] + sm[3]);

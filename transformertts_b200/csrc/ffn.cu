@@ -116,8 +116,7 @@ ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
   cluster_sync_all();                   // the peer's barriers are initialised before anything is signalled on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  griddep_launch();
-  griddep_wait();
+  griddep_launch();                     // the producer thread alone waits for the previous grid (see below)
   const uint32_t t_y = tmem_base + 256;
   // The two CTAs of a cluster work on neighbouring row tiles in lock step: one 256-row MMA stream issued by rank 0.
   const int pair = static_cast<int>(blockIdx.x >> 1);
@@ -137,26 +136,42 @@ ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUte
         return smem + RING_OFF + slot * BLK;
       };
       auto advance = [&]() { if (++slot == NSLOT) { slot = 0; sph ^= 1; } };
+      // The W blocks of a tile in the order the MMA thread consumes them: for hidden chunk hc = 0 .. NHC: two W1 blocks of
+      // chunk hc (hc < NHC), then two W2 blocks of chunk hc - 1 (hc >= 1).
+      int hc = 0, step = 0;                             // position in that sequence
+      auto emit_next = [&]() -> bool {                  // issues the next block; false when the tile's sequence is over
+        for (;;) {
+          if (hc > NHC) return false;
+          const int st = step;
+          const int h = hc;
+          if (++step == 4) { step = 0; ++hc; }
+          if (st < 2 && h < NHC) {                      // W1 rows h*128 + 64 r .. + 63, k-blocks 2 st and 2 st + 1
+            uint8_t* dst = next();
+            tma_load_3d_cg2(dst, &tmW1, bar0(w_full + slot), (2 * st) * BK, h * HC + r * 64, 0);
+            tma_load_3d_cg2(dst + BLK / 2, &tmW1, bar0(w_full + slot), (2 * st + 1) * BK, h * HC + r * 64, 0);
+            advance();
+            return true;
+          }
+          if (st >= 2 && h >= 1) {                      // W2 rows 128 r .. + 127, hidden columns of chunk h - 1
+            uint8_t* dst = next();
+            tma_load_3d_cg2(dst, &tmW2, bar0(w_full + slot), (h - 1) * HC + (st - 2) * BK, r * 128, 0);
+            advance();
+            return true;
+          }
+        }
+      };
+      // Programmatic dependent launch: the weights are written by no kernel, so the ring is filled BEFORE waiting for
+      // the previous grid (whose output is this kernel's x); the other roles touch nothing of that grid except through x.
+      if (more(0))
+        for (int i = 0; i < NSLOT; ++i) emit_next();
+      griddep_wait();
       for (int it = 0; more(it); ++it) {
         const int tile = tile_of(it);
         mbar_wait(x_empty, (it & 1) ^ 1);
         if (r == 0) mbar_expect_tx(x_full, 2 * 4 * BLK);
         for (int kb = 0; kb < 4; ++kb) tma_load_3d_cg2(smem + X_OFF + kb * BLK, &tmX, bar0(x_full), kb * BK, tile * BM, 0);
-        for (int hc = 0; hc <= NHC; ++hc) {
-          if (hc < NHC)
-            for (int h2 = 0; h2 < 2; ++h2) {            // W1 rows hc*128 + 64 r .. + 63, k-blocks 2 h2 and 2 h2 + 1
-              uint8_t* dst = next();
-              tma_load_3d_cg2(dst, &tmW1, bar0(w_full + slot), (2 * h2) * BK, hc * HC + r * 64, 0);
-              tma_load_3d_cg2(dst + BLK / 2, &tmW1, bar0(w_full + slot), (2 * h2 + 1) * BK, hc * HC + r * 64, 0);
-              advance();
-            }
-          if (hc >= 1)
-            for (int kb2 = 0; kb2 < 2; ++kb2) {         // W2 rows 128 r .. + 127, hidden columns of chunk hc - 1
-              uint8_t* dst = next();
-              tma_load_3d_cg2(dst, &tmW2, bar0(w_full + slot), (hc - 1) * HC + kb2 * BK, r * 128, 0);
-              advance();
-            }
-        }
+        while (emit_next()) {}
+        hc = 0; step = 0;
       }
     }
     __syncwarp();

@@ -174,7 +174,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   griddep_launch();
-  griddep_wait();                       // activations of the previous kernel are complete and visible from here on
+  // Programmatic dependent launch: only the producer thread reads what the previous kernel wrote (activation and
+  // residual tiles), so only it waits for that grid -- AFTER it has issued the loads of the resident W slice, which no
+  // kernel writes: the 128 KB (1.2 us) of weights arrive while the tail of the previous grid drains.  Everything the
+  // other roles touch is ordered behind those loads through the full / acc_full barriers.
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
@@ -191,6 +194,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         for (int kb = 0; kb < p.num_kb; ++kb)
           load(smem + kb * P::WB, &tmW, w_full, kb * BK, ws_n * BN + rank * (BN / 2), 0);
       }
+      griddep_wait();                   // activations of the previous kernel are complete and visible from here on
       int s = 0; uint32_t ph = 0;
       int m_tile, n_tile;
       for (int i = 0; tile_at(i, m_tile, n_tile); ++i) {
