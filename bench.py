@@ -557,16 +557,18 @@ def run_ours(args):
         return {"value": total_valid / sec, "ms_per_step": sec * 1e3, "h2d_bytes_per_step": bytes_io[0],
                 "d2h_bytes_per_step": bytes_io[1], "runs_ms_per_step": [x * 1e3 for x in runs]}
 
-    e2e_main = e2e_variant(host_b16, check=True)
-    e2e_variants = {}
+    # headline: the reference's own step around forward -- LightningModule.validation_step (lightning_module.py:102-130):
+    # batch to the device, forward, criterion on the device, the loss scalars back to the host (`.item()`); the outputs
+    # and alignments stay on the device (utils/plot.py pulls single maps once per epoch)
+    e2e_main = e2e_variant(host_f32, loss_only=True)
+    e2e_variants = {"outputs_f32_d2h": e2e_variant(host_b16, check=True)}     # round-1 definition: pred | post | stop to the host
     if not args.no_extra:
-        e2e_variants = {
-            "f32_mel_in_f32_out": e2e_variant(host_f32, check=True),
-            "bf16_mel_in_bf16_packed_out": e2e_variant(host_b16, out_dtype=torch.bfloat16),
-            "validation_step_loss_only": e2e_variant(host_f32, loss_only=True),
-            "with_alignments_d2h": e2e_variant(host_b16, with_align=True),
+        e2e_variants.update({
+            "outputs_f32_d2h_f32_mel_in": e2e_variant(host_f32, check=True),
+            "outputs_bf16_packed_d2h": e2e_variant(host_b16, out_dtype=torch.bfloat16),
+            "outputs_and_alignments_d2h": e2e_variant(host_b16, with_align=True),
             "copy_only_probe": e2e_variant(host_b16, compute=False),
-        }
+        })
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- configs[0] (B=16, Tp=150, Tm=800) on the GPU: the same-config counterpart of the CPU arm's step
@@ -755,13 +757,14 @@ def run_ours(args):
             "frames": {"valid_frames_per_step": total_valid, "padded_frames_per_step": total_padded,
                        "padded_frames_per_s": total_padded / (ms_step / 1e3)},
             "e2e": dict(e2e_main, unit="valid mel frames/s",
-                        note="median of 3 runs of K steps through transformertts_b200.data.PinnedFeeder / OutputFetcher: every "
-                             "step a collated pinned host batch (bf16 target mel, as data.collate_fn(mel_dtype=bfloat16) "
-                             "yields; the kernels round the mel to bf16 either way and the result is bit-identical) -> device "
-                             "on a copy stream, forward through the public module API, pred | post | stop (fp32, one "
-                             "allocation) -> pinned host with one copy on a third stream; double-buffered; the fetched "
-                             "tensors are checked bit-equal against the device-resident run; alignments stay on the device "
-                             "as in the reference (utils/plot.py copies single maps); see e2e_variants for the other mixes"),
+                        note="median of 3 runs of K steps of the reference's validation step (lightning_module.py:102-130) "
+                             "through the package's public API: every step a collated pinned host batch (fp32 mel) -> device on "
+                             "a copy stream (transformertts_b200.data.PinnedFeeder, double-buffered), TransformerTTS.forward "
+                             "with alignments, TransformerTTSLoss on the device, the four loss scalars -> pinned host; the "
+                             "outputs stay on the device as in the reference.  e2e_variants.outputs_f32_d2h is the round-1 "
+                             "definition (pred | post | stop fp32 copied to the host every step, one copy, checked bit-equal "
+                             "against the device-resident run); the other variants change the bytes that travel; "
+                             "copy_only_probe runs the same copies without the forward (the host-side limit at N = 8)"),
             "e2e_variants": e2e_variants, "cfg1_b16": cfg1,
             "gpu_launches": launches,
             "roofline": roofline, "kernels": kernels, "step_roofline": step_roofline,
