@@ -16,7 +16,7 @@
  *   tts_teacher_forcing_mix   block_mask + apply_teacher_forcing  utils/util.py:103-120
  *   tts_loss             TransformerTTSLoss.forward              loss.py:15-55
  *   tts_pack_outputs     (no reference counterpart) pred/post/stop -> one bf16 buffer for a single D2H copy
- *   tts_op_linear / tts_op_conv1d / tts_op_attention / tts_op_ffn
+ *   tts_op_linear / tts_op_linear_chain / tts_op_conv1d / tts_op_attention / tts_op_ffn
  *                        the torch.nn operators underneath (model/module.py:4-53,
  *                        torch/nn/functional.py:5798,6620-6665), exported for per-operator parity tests
  */
@@ -166,6 +166,16 @@ int tts_pack_outputs(const float* pred, const float* post, const float* stop, lo
 int tts_op_linear(const void* A, const void* W, const float* bias, int M, int N, int K, int act,
                   const float* pe, float alpha, int pe_period, const void* residual, const float* ln_g,
                   const float* ln_b, void* out_bf16, float* out_f32, void* stream);
+
+/* Two chained GEMMs in one launch (N = 256 both, K1 <= 256, M >= 129):
+ *   y1 = LayerNorm(residual + A W1^T + b1) when ln_g != NULL (act1 must be 0), else act1(A W1^T + b1);
+ *   out2 = act2(y1_bf16 W2^T + b2) + alpha * pe[row % pe_period]   (pe may be NULL).
+ * y1 stays on the SM (bf16, tensor memory) as the A operand of the second GEMM; it is also stored to out1_bf16 unless
+ * that is NULL.  This is how tts_forward runs out-projection + LayerNorm -> cross-attention Q projection and
+ * prenet 1 -> prenet 2 + PE. */
+int tts_op_linear_chain(const void* A, const void* W1, const float* b1, int M, int K1, int act1, const void* residual,
+                        const float* ln_g, const float* ln_b, const void* W2, const float* b2, int act2,
+                        const float* pe, float alpha, int pe_period, void* out1_bf16, void* out2_bf16, void* stream);
 
 /* Conv1d(kernel `taps`, zero padding (taps-1)/2) over x bf16 [B][T][C] with W bf16 [N][taps][Cpad]
  * (Cpad = C rounded up to 64), + bias, act; optional f32 residual [B][T][N]. */

@@ -93,6 +93,28 @@ def ref_linear(A, W, bias, act=0, pe=None, alpha=0.0, pe_period=0, residual=None
     return y.float()
 
 
+def op_linear_chain(A, W1, b1, W2, b2, act1=0, residual=None, ln=None, act2=0, pe=None, alpha=0.0, pe_period=0, store1=True):
+    """Two chained GEMMs in one launch (tts_op_linear_chain).  Returns (y1 or None, out2) as fp32 cpu tensors."""
+    lib = _ext.load()
+    M, K = A.shape
+    Kp = (K + 63) // 64 * 64
+    Ad = torch.zeros(M, Kp); Ad[:, :K] = A
+    W1d = torch.zeros(256, Kp); W1d[:, :K] = W1
+    Ad, W1d, W2d = dev_bf16(Ad), dev_bf16(W1d), dev_bf16(W2)
+    b1d, b2d = dev_f32(b1), dev_f32(b2)
+    rd = dev_bf16(residual) if residual is not None else None
+    g = dev_f32(ln[0]) if ln is not None else None
+    b = dev_f32(ln[1]) if ln is not None else None
+    ped = dev_f32(pe) if pe is not None else None
+    o1 = torch.full((M, 256), float("nan"), dtype=torch.bfloat16, device=DEV) if store1 else None
+    o2 = torch.full((M, 256), float("nan"), dtype=torch.bfloat16, device=DEV)
+    _ext.check(lib.tts_op_linear_chain(_ext.ptr(Ad), _ext.ptr(W1d), _ext.ptr(b1d), M, Kp, act1, _ext.ptr(rd), _ext.ptr(g),
+                                       _ext.ptr(b), _ext.ptr(W2d), _ext.ptr(b2d), act2, _ext.ptr(ped), float(alpha),
+                                       int(pe_period), _ext.ptr(o1), _ext.ptr(o2), stream()), "tts_op_linear_chain")
+    torch.cuda.synchronize()
+    return (o1.float().cpu() if store1 else None), o2.float().cpu()
+
+
 def op_conv1d(x, w, bias, act=0, residual=None, want_f32=False):
     """x [B,T,C], w [N,C,taps] (torch Conv1d layout) fp32 cpu (bf16-representable)."""
     lib = _ext.load()

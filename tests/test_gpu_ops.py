@@ -4,8 +4,8 @@ accumulation-order noise; fp32 outputs only the latter."""
 import pytest
 import torch
 
-from parity_common import (bf16r, op_attention, op_conv1d, op_ffn, op_linear, ref_attention, ref_conv1d, ref_ffn,
-                           ref_linear, report)
+from parity_common import (bf16r, op_attention, op_conv1d, op_ffn, op_linear, op_linear_chain, ref_attention, ref_conv1d,
+                           ref_ffn, ref_linear, report)
 
 pytestmark = pytest.mark.gpu
 
@@ -85,6 +85,37 @@ def test_linear_relu_positional_encoding():
     o16, _ = op_linear(A, W, b, act=1, pe=pe, alpha=0.7, pe_period=T)
     ref = ref_linear(A, W, b, act=1, pe=pe, alpha=0.7, pe_period=T)
     _check("linear+relu+PE bf16", o16, ref, BF16_ATOL, BF16_RTOL)
+
+
+# ------------------------------------------------------------------ two chained GEMMs in one launch
+@pytest.mark.parametrize("M", [129, 256, 1000, 20000])
+def test_linear_chain_residual_layernorm_then_projection(M):
+    """out-projection + residual + LayerNorm -> cross-attention Q projection (c_api.cu run_decoder)."""
+    g = torch.Generator().manual_seed(M)
+    A, W1, b1 = _rand((M, 256), g), _rand((256, 256), g, 1 / 16), torch.randn(256, generator=g) * 0.1
+    res = _rand((M, 256), g)
+    ln = (1 + 0.1 * torch.randn(256, generator=g), 0.05 * torch.randn(256, generator=g))
+    W2, b2 = _rand((256, 256), g, 1 / 16), torch.randn(256, generator=g) * 0.1
+    y1, o2 = op_linear_chain(A, W1, b1, W2, b2, residual=res, ln=ln)
+    r1 = ref_linear(A, W1, b1, residual=res, ln=ln)
+    _check("chain y1 (LN) bf16", y1, r1, BF16_ATOL, BF16_RTOL)
+    r2 = ref_linear(bf16r(r1), W2, b2)          # the second GEMM consumes the bf16-rounded first result
+    _check("chain out2 bf16", o2, r2, 6e-3, BF16_RTOL)
+
+
+@pytest.mark.parametrize("M,T", [(3 * 70, 70), (2 * 800, 800)])
+def test_linear_chain_prenet(M, T):
+    """prenet 1 (K = 80 padded to 128, ReLU) -> prenet 2 (ReLU) + alpha * PE, first result not stored."""
+    import tts_oracle as O
+    g = torch.Generator().manual_seed(M + 1)
+    A, W1, b1 = _rand((M, 80), g), _rand((256, 80), g, 80 ** -0.5), torch.randn(256, generator=g) * 0.1
+    W2, b2 = _rand((256, 256), g, 1 / 16), torch.randn(256, generator=g) * 0.1
+    pe = O.pe_table()
+    y1, o2 = op_linear_chain(A, W1, b1, W2, b2, act1=1, act2=1, pe=pe, alpha=0.7, pe_period=T, store1=False)
+    assert y1 is None
+    r1 = ref_linear(A, W1, b1, act=1)
+    r2 = ref_linear(bf16r(r1), W2, b2, act=1, pe=pe, alpha=0.7, pe_period=T)
+    _check("chain prenet out2 bf16", o2, r2, 6e-3, BF16_RTOL)
 
 
 # ------------------------------------------------------------------ fused FFN block (two GEMMs + residual + LayerNorm)

@@ -54,6 +54,23 @@ def linear(M, N, K, act=0, ln=False, pe=False, f32=False):
     return fn, 2.0 * M * N * K
 
 
+def chain(M, K1, ln=False, pe=False, store1=True):
+    A, W1, b1 = bf(M, K1), bf(256, K1, scale=K1 ** -0.5), torch.zeros(256, device=dev)
+    W2, b2 = bf(256, 256, scale=1 / 16), torch.zeros(256, device=dev)
+    res = bf(M, 256) if ln else None
+    g = torch.ones(256, device=dev) if ln else None
+    bb = torch.zeros(256, device=dev) if ln else None
+    pet = torch.randn(5000, 256, device=dev) if pe else None
+    o1 = torch.empty(M, 256, dtype=torch.bfloat16, device=dev) if store1 else None
+    o2 = torch.empty(M, 256, dtype=torch.bfloat16, device=dev)
+
+    def fn():
+        _ext.check(lib.tts_op_linear_chain(P(A), P(W1), P(b1), M, K1, 0 if ln else 1, P(res), P(g), P(bb), P(W2), P(b2),
+                                           1 if pe else 0, P(pet), 0.7, 800 if pe else 0, P(o1), P(o2), st()), "chain")
+    fn.keep = (A, W1, b1, W2, b2, res, g, bb, pet, o1, o2)
+    return fn, 2.0 * M * 256 * (K1 + 256)
+
+
 def ffn(M):
     x, w1, w2 = bf(M, 256), bf(1024, 256, scale=1 / 16), bf(256, 1024, scale=1 / 32)
     b1, b2, g, b = (torch.zeros(1024, device=dev), torch.zeros(256, device=dev), torch.ones(256, device=dev),
@@ -115,6 +132,8 @@ OPS = [
     ("dec out+LN 51200x256x256", lambda: linear(Nm, 256, 256, ln=True), 6),
     ("dec cq 51200x256x256", lambda: linear(Nm, 256, 256), 3),
     ("dec ckv 9600x512x256", lambda: linear(Np, 512, 256), 3),
+    ("chain dec out+LN -> cq 51200 (one launch for the two above)", lambda: chain(Nm, 256, ln=True), 0),
+    ("chain dec prenet1 -> prenet2+PE 51200", lambda: chain(Nm, 128, pe=True, store1=False), 0),
     ("dec cross-attn 800x150 +probs", lambda: attn(Tm, Tp, 0, True, False), 3),
     ("dec ffn fused 51200x256->1024->256 +LN", lambda: ffn(Nm), 3),
     ("dec ffn1 51200x1024x256 (unfused, not in the forward)", lambda: linear(Nm, 1024, 256, act=1), 0),

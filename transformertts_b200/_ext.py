@@ -68,6 +68,8 @@ SIGNATURES = {
     "tts_pack_outputs": (C.c_int, [vp, vp, vp, C.c_longlong, vp, vp]),
     "tts_op_linear": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_int, vp, vp, vp,
                                 vp, vp, vp]),
+    "tts_op_linear_chain": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, C.c_int, vp, C.c_float, C.c_int,
+                                      vp, vp, vp]),
     "tts_op_conv1d": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]),
     "tts_op_ffn": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, C.c_int, vp, vp]),
     "tts_op_attention": (C.c_int, [vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int,

@@ -180,6 +180,24 @@ extern "C" int tts_op_linear(const void* A, const void* W, const float* bias, in
   return 0;
 }
 
+extern "C" int tts_op_linear_chain(const void* A, const void* W1, const float* b1, int M, int K1, int act1, const void* residual,
+                                   const float* ln_g, const float* ln_b, const void* W2, const float* b2, int act2,
+                                   const float* pe, float alpha, int pe_period, void* out1_bf16, void* out2_bf16,
+                                   void* stream) {
+  if (K1 % 64 != 0) return fail("tts_op_linear_chain: K1 must be a multiple of 64");
+  GemmArgs g = linear_args((const bf16*)A, M, K1, W1, b1, kD);
+  g.act = act1;
+  g.residual = (const bf16*)residual; g.ld_res = kD;
+  g.ln_g = ln_g; g.ln_b = ln_b;
+  g.out_bf16 = (bf16*)out1_bf16; g.ld_bf16 = kD;
+  g.W2 = (const bf16*)W2; g.bias2 = b2; g.act2 = act2;
+  g.pe = pe; g.alpha = alpha; g.pe_period = pe_period;
+  g.out2 = (bf16*)out2_bf16; g.ld_out2 = kD;
+  if (!gemm2_chain_supports(g)) return fail("tts_op_linear_chain: unsupported shape (K1 <= 256, N = 256, >= 129 rows, aligned)");
+  TRY(gemm2_chain_launch(g, (cudaStream_t)stream));
+  return 0;
+}
+
 extern "C" int tts_op_conv1d(const void* x, const void* W, const float* bias, int B, int T, int C, int N, int taps,
                              int act, const float* residual_f32, void* out_bf16, float* out_f32, void* stream) {
   GemmArgs g = conv_args((const bf16*)x, B, T, C, W, bias, N, taps, -((taps - 1) / 2));
@@ -223,6 +241,20 @@ static const char* run_attention(const bf16* q, int ldq, const bf16* k, const bf
   a.O = out; a.ldo = kD; a.probs = probs; a.klen = klen;
   a.B = B; a.Tq = Tq; a.Tk = Tk; a.causal = causal;
   return attn_launch(a, s);
+}
+
+// TTS_GEMM_CHAIN=1: run  out-projection + LayerNorm -> cross-attention Q projection  and  prenet 1 -> prenet 2 + PE  as
+// ONE chained launch each (gemm2.cu CHAIN plan: the intermediate activation stays in tensor memory).  Measured and NOT the
+// default (profiles/r02_gemm_chain_ab.txt): alone, between L2 flushes, a chained launch beats its two kernels (41.0 vs
+// 26.2 + 19.2 us; 42.2 vs 15.9 + 32.6 us), but inside the forward the two-kernel sequence wins (1.128 vs 1.171 ms per
+// cfg-2 forward): the 26 MB intermediate is L2-resident for the second kernel anyway, and the chained tile is one serial
+// chain (GEMM 1 -> two-pass LayerNorm epilogue -> GEMM 2 -> epilogue 2) on a 3-stage ring where the separate kernels
+// overlap tile i's epilogue with tile i+1's MMAs on a 7-stage ring.  Kept under test (tests/test_gpu_ops.py,
+// tests/test_gpu_pair_plans.py) as the starting point for a chained plan with two tiles in flight.
+static bool chain_enabled() {
+  static const char* env = getenv("TTS_GEMM_CHAIN");
+  static const bool on = env != nullptr && env[0] == '1';
+  return on;
 }
 
 // out = LayerNorm(res + A . W^T + b)
@@ -376,12 +408,22 @@ static const char* run_decoder(const TtsWeights* w, const void* mel, int flags, 
   {
     // decoder prenet on the go-frame-shifted target (model/model.py:278-279, 297): frame t reads mel[t-1]
     GemmArgs g = conv_args(mel16, nb, Tm, kMel, w->pre1_w, w->pre1_b, kD, 1, -1);
-    g.act = ACT_RELU; g.out_bf16 = d0; g.ld_bf16 = kD;
-    if ((e = gemm_launch(g, s))) return e;
-    GemmArgs h = linear_args(d0, Nm, kD, w->pre2_w, w->pre2_b, kD);
-    h.act = ACT_RELU; h.pe = w->pe; h.alpha = w->alpha; h.pe_period = Tm;
-    h.out_bf16 = d1; h.ld_bf16 = kD;
-    if ((e = gemm_launch(h, s))) return e;
+    g.act = ACT_RELU;
+    // prenet 1 -> prenet 2 + PE chained in one launch (the hidden activation stays in tensor memory)
+    g.W2 = (const bf16*)w->pre2_w; g.bias2 = w->pre2_b; g.act2 = ACT_RELU;
+    g.pe = w->pe; g.alpha = w->alpha; g.pe_period = Tm;
+    g.out2 = d1; g.ld_out2 = kD;
+    if (chain_enabled() && gemm2_chain_supports(g)) {
+      if ((e = gemm2_chain_launch(g, s))) return e;
+    } else {
+      g.W2 = nullptr; g.pe = nullptr; g.out2 = nullptr;
+      g.out_bf16 = d0; g.ld_bf16 = kD;
+      if ((e = gemm_launch(g, s))) return e;
+      GemmArgs h = linear_args(d0, Nm, kD, w->pre2_w, w->pre2_b, kD);
+      h.act = ACT_RELU; h.pe = w->pe; h.alpha = w->alpha; h.pe_period = Tm;
+      h.out_bf16 = d1; h.ld_bf16 = kD;
+      if ((e = gemm_launch(h, s))) return e;
+    }
   }
   bf16* x = d1; bf16* y = d0;
   bool joined = enc_join == nullptr;
@@ -391,8 +433,20 @@ static const char* run_decoder(const TtsWeights* w, const void* mel, int flags, 
     const TtsDecLayerW& L = w->dec[l];
     if ((e = proj(x, Nm, kD, L.sa.w_in, L.sa.b_in, 3 * kD, ACT_NONE, qkv, s))) return e;
     if ((e = run_attention(qkv, 3 * kD, qkv + kD, qkv + 2 * kD, 3 * kD, att, nullptr, mel_len, nb, Tm, Tm, 1, s))) return e;
-    if ((e = proj_res_ln(att, Nm, kD, L.sa.w_out, L.sa.b_out, x, L.ln1, y, s))) return e;            // y = LN1
-    if ((e = proj(y, Nm, kD, L.ca.w_in, L.ca.b_in, kD, ACT_NONE, cq, s))) return e;
+    {                                                // y = LN1(x + att Wo^T + b), cq = y Wq^T + bq: one chained launch
+      GemmArgs g = linear_args(att, Nm, kD, L.sa.w_out, L.sa.b_out, kD);
+      g.residual = x; g.ld_res = kD;
+      g.ln_g = L.ln1.g; g.ln_b = L.ln1.b;
+      g.out_bf16 = y; g.ld_bf16 = kD;
+      g.W2 = (const bf16*)L.ca.w_in; g.bias2 = L.ca.b_in; g.act2 = ACT_NONE;
+      g.out2 = cq; g.ld_out2 = kD;
+      if (chain_enabled() && gemm2_chain_supports(g)) {
+        if ((e = gemm2_chain_launch(g, s))) return e;
+      } else {
+        if ((e = proj_res_ln(att, Nm, kD, L.sa.w_out, L.sa.b_out, x, L.ln1, y, s))) return e;
+        if ((e = proj(y, Nm, kD, L.ca.w_in, L.ca.b_in, kD, ACT_NONE, cq, s))) return e;
+      }
+    }
     if (!joined) {                                   // first use of the encoder branch's results
       if (cudaStreamWaitEvent(s, enc_join, 0) != cudaSuccess) return "side stream join failed";
       joined = true;

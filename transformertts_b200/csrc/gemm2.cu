@@ -39,12 +39,18 @@ constexpr int CHUNK32_BYTES = BM * 32 * 4;         // 16 KB
 // PAIR: two CTAs of a cluster share one 256 x 256 output tile pair (tcgen05 cta_group::2, M = 256).  Each CTA loads
 // its own 128 rows of A and only HALF of the W rows, so a streamed k-block is 32 KB instead of 48 KB and a resident W
 // slice 64 KB instead of 128 KB; the bytes saved become ring stages (the kernels are operand-delivery bound).
-template <bool LN, bool WS, bool F32 = false, bool PAIR = false>
+// CHAIN (W-stationary CTA pairs only): two GEMMs per row tile in one launch,  out2 = epi2( epi1(A W1^T) W2^T ), N = K2 = 256.
+// The first result (after bias / ReLU or residual + LayerNorm) is packed to bf16 into the tensor-memory columns its
+// accumulator came from and feeds the second GEMM as the A operand (tcgen05.mma with A in TMEM); W1 and W2 are both
+// resident.  Used for  out-projection + residual + LayerNorm -> cross-attention Q projection  and  prenet 1 -> prenet 2
+// + PE: one launch, one prologue / tail and no round trip of the intermediate activation instead of two of each.
+template <bool LN, bool WS, bool F32 = false, bool PAIR = false, bool CHAIN = false>
 struct Plan {
   static_assert(!F32 || (!LN && !WS && !PAIR), "the fp32-output plan streams W, has no LayerNorm and no CTA pairs");
+  static_assert(!CHAIN || (WS && PAIR && !F32), "chained GEMMs run on W-stationary CTA pairs");
   static constexpr int WB = PAIR ? B_BYTES / 2 : B_BYTES;            // one W k-block as this CTA holds it
-  static constexpr int W_BYTES = WS ? 4 * WB : 0;
-  static constexpr int ST = PAIR ? (WS ? (LN ? 7 : 8) : 5) : (WS ? (LN ? 3 : 4) : (F32 ? 5 : 3));
+  static constexpr int W_BYTES = WS ? (CHAIN ? 8 : 4) * WB : 0;      // CHAIN: W1 in k-block slots 0..3, W2 in 4..7
+  static constexpr int ST = CHAIN ? 3 : (PAIR ? (WS ? (LN ? 7 : 8) : 5) : (WS ? (LN ? 3 : 4) : (F32 ? 5 : 3)));
   static constexpr int STAGE_BYTES = WS ? A_BYTES : A_BYTES + (F32 ? WB / 2 : WB);   // F32: N <= 128, half a W block
   static constexpr int RING_OFF = W_BYTES;
   static constexpr int NBUF_H = (WS || F32) ? 2 : 3;                // staging buffers per epilogue half
@@ -54,7 +60,8 @@ struct Plan {
   static constexpr int BAR_OFF = ID_OFF + (LN ? 8192 : 0);
   static constexpr int PAR_OFF = BAR_OFF + 256;
   static constexpr int NBIAS = (WS || LN) ? BN : MAX_N;
-  static constexpr int TOTAL = PAR_OFF + (NBIAS + (LN ? 2 * BN : 0)) * 4 + (LN ? 4096 : 0) + 1024;  // + LN row partials
+  static constexpr int BIAS2_OFF = PAR_OFF + (NBIAS + (LN ? 2 * BN : 0)) * 4 + (LN ? 4096 : 0);   // after the LN row partials
+  static constexpr int TOTAL = BIAS2_OFF + (CHAIN ? BN * 4 : 0) + 1024;
   static_assert(TOTAL <= 232448, "shared memory plan exceeds 227 KB");
 };
 
@@ -70,6 +77,9 @@ struct Dev {
   int n_mma, w_stage_bytes, n_main, has_bf16;      // MMA N (multiple of 16), bytes of one W k-block, columns stored
   const float* res32; int ld_res32;                // fp32 residual [B*T][ld_res32] or null
   float* out_last;                                 // column N-1 -> out_last[row] (stop head) or null
+  // chained plan only: second GEMM's bias / activation (pe / alpha / pe_period above apply to ITS epilogue), and whether
+  // the first result is also stored (through tmO; the second leaves through tmO2)
+  const float* bias2; int act2; int store1;
 };
 }  // namespace g2
 
@@ -87,12 +97,14 @@ __device__ __forceinline__ void for_chunks4(uint32_t taddr, F&& f) {
   tmem_ld_wait(); f(3, rb);
 }
 
-template <bool LN, bool WS, bool F32, bool PAIR>
+template <bool LN, bool WS, bool F32, bool PAIR, bool CHAIN>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const Dev p) {
-  // tmO: bf16 output (may be unused when F32 && !has_bf16); tmR: bf16 residual (LN) or the fp32 output (F32)
-  using P = Plan<LN, WS, F32, PAIR>;
+             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR,
+             const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmO2, const Dev p) {
+  // tmO: bf16 output (may be unused when F32 && !has_bf16); tmR: bf16 residual (LN) or the fp32 output (F32);
+  // tmW2 / tmO2: second weight matrix / second output of the chained plan (copies of tmW / tmO otherwise)
+  using P = Plan<LN, WS, F32, PAIR, CHAIN>;
   constexpr int ST = P::ST;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
@@ -105,6 +117,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   float* s_bias = reinterpret_cast<float*>(smem + P::PAR_OFF);   // [NBIAS]
   float* s_lng = s_bias + P::NBIAS;                              // [256]
   float* s_lnb = s_lng + BN;                                     // [256]
+  float* s_bias2 = reinterpret_cast<float*>(smem + P::BIAS2_OFF);  // [256] (CHAIN)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -138,6 +151,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tma_prefetch_desc(&tmW);
     tma_prefetch_desc(&tmO);
     if (LN) tma_prefetch_desc(&tmR);
+    if (CHAIN) { tma_prefetch_desc(&tmW2); tma_prefetch_desc(&tmO2); }
     for (int s = 0; s < ST; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, 1); }
     // PAIR: the epilogue warps hand the accumulator back on their own CTA's barrier (a cluster-scope arrive costs
     // ~1000 cycles); rank 1's otherwise idle warp 1 waits there and forwards one arrive to the issuer in rank 0
@@ -153,6 +167,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const int nb0 = WS ? ws_n * BN : 0;
     const int nb = WS ? BN : (F32 ? BN : p.N);
     for (int i = threadIdx.x - 64; i < nb; i += 256) s_bias[i] = (!F32 || i < p.N) ? __ldg(p.bias + nb0 + i) : 0.f;
+    if (CHAIN)
+      for (int i = threadIdx.x - 64; i < BN; i += 256) s_bias2[i] = __ldg(p.bias2 + i);
     if (LN) {
       for (int i = threadIdx.x - 64; i < BN; i += 256) { s_lng[i] = __ldg(p.ln_g + i); s_lnb[i] = __ldg(p.ln_b + i); }
       // 64x64 identity in the K-major SWIZZLE_128B operand layout: the residual tile is added to the accumulator
@@ -190,9 +206,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         else tma_load_3d(dst, tm, bar, c0, c1, c2);
       };
       if (WS) {
-        if (rank == 0) mbar_expect_tx(w_full, p.num_kb * P::WB * nload);
+        if (rank == 0) mbar_expect_tx(w_full, (p.num_kb + (CHAIN ? 4 : 0)) * P::WB * nload);
         for (int kb = 0; kb < p.num_kb; ++kb)
           load(smem + kb * P::WB, &tmW, w_full, kb * BK, ws_n * BN + rank * (BN / 2), 0);
+        if (CHAIN)
+          for (int kb = 0; kb < 4; ++kb)
+            load(smem + (4 + kb) * P::WB, &tmW2, w_full, kb * BK, rank * (BN / 2), 0);
       }
       griddep_wait();                   // activations of the previous kernel are complete and visible from here on
       int s = 0; uint32_t ph = 0;
@@ -230,10 +249,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       int m_tile, n_tile;
       if (WS) { mbar_wait(w_full, 0); tc_fence_after(); }
       for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
-        const int buf = it & 1;
+        const int buf = CHAIN ? 0 : (it & 1);
         const uint32_t use = static_cast<uint32_t>(it >> 1);
-        mbar_wait(acc_empty + buf, (use & 1) ^ 1);           // epilogue has drained this TMEM buffer
-        tc_fence_after();
+        // CHAIN: GEMM 1 always accumulates into buffer 0 and needs no wait: the bf16 A operand of the previous tile's
+        // GEMM 2 sits in the same columns, but that GEMM 2 was issued before (the tensor pipe runs in order), and it was
+        // issued only after epilogue 1 of that tile had read the accumulator out
+        if (!CHAIN) { mbar_wait(acc_empty + buf, (use & 1) ^ 1); tc_fence_after(); }   // epilogue has drained this TMEM buffer
         const uint32_t tacc = tmem_base + buf * BN;
         const int total_kb = p.num_kb + (LN ? 4 : 0);
         for (int kb = 0; kb < total_kb; ++kb) {
@@ -257,6 +278,21 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           if (kb == total_kb - 1) commit(acc_full + buf);
           if (++s == ST) { s = 0; ph ^= 1; }
         }
+        if constexpr (CHAIN) {
+          // GEMM 2: A = the tile's first result as bf16 in TMEM columns [0, 128) (two K neighbours per column),
+          // B = the resident W2, accumulator = buffer 1
+          mbar_wait(acc_empty, it & 1);                      // epilogue 1 of this tile has stored the A operand
+          mbar_wait(acc_empty + 1, (it & 1) ^ 1);            // epilogue 2 of the previous tile has drained buffer 1
+          tc_fence_after();
+          const uint32_t idesc2 = umma_idesc_bf16(2 * BM, BN);
+          for (int kb = 0; kb < 4; ++kb) {
+            const uint64_t db = umma_desc_sw128(smem_u32(smem + (4 + kb) * P::WB));
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+              tc_mma_bf16_cg2_ts(tmem_base + BN, tmem_base + kb * 32 + k * 8, db + 2 * k, idesc2, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          commit(acc_full + 1);
+        }
       }
     }
     if (PAIR && lane == 0 && rank == 1) {
@@ -264,9 +300,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       const uint32_t remote = mapa_u32(smem_u32(acc_empty), 0);
       int m_tile, n_tile;
       for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
-        const int buf = it & 1;
-        mbar_wait(acc_empty + buf, (it >> 1) & 1);
-        mbar_arrive_cluster(remote + buf * 8);
+        if constexpr (CHAIN) {                               // both buffers are handed back once per tile
+          mbar_wait(acc_empty, it & 1);
+          mbar_arrive_cluster(remote);
+          mbar_wait(acc_empty + 1, it & 1);
+          mbar_arrive_cluster(remote + 8);
+        } else {
+          const int buf = it & 1;
+          mbar_wait(acc_empty + buf, (it >> 1) & 1);
+          mbar_arrive_cluster(remote + buf * 8);
+        }
       }
     }
     __syncwarp();
@@ -377,6 +420,144 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           }
           ++kc;
         }
+      }
+      if (leader) bulk_wait<0>();
+    } else if constexpr (CHAIN) {
+      // ---- chained plan: epilogue 1 (bias + act, or residual + LayerNorm) -> bf16 -> [TMA store] + A operand of GEMM 2
+      // in TMEM -> epilogue 2 (bias + act + PE) -> bf16 -> TMA store.  thread == (output row, column half), as below.
+      uint8_t* bufs = smem + P::SLAB_OFF + half * (NB * CHUNK_BYTES);
+      const uint32_t sw = static_cast<uint32_t>((row >> 1) & 3);
+      uint8_t* my_row = bufs + row * 64;
+      float2* s_stat = reinterpret_cast<float2*>(s_lnb + BN);
+      const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+      int kc = 0;
+      auto stage_and_store = [&](const CUtensorMap* tm, const uint32_t (&pk)[16], int c, int t0, int b) {
+        const int bi = kc % NB;
+        uint8_t* ws = my_row + bi * CHUNK_BYTES;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<uint4*>(ws + ((static_cast<uint32_t>(j) ^ sw) << 4)) =
+              make_uint4(pk[j * 4], pk[j * 4 + 1], pk[j * 4 + 2], pk[j * 4 + 3]);
+        fence_proxy_async();
+        if (leader) bulk_wait_read<NB - 2>();
+        named_bar_sync(1 + half, 128);
+        if (leader) {
+          tma_store_3d(tm, bufs + bi * CHUNK_BYTES, c * 32, t0, b);
+          bulk_commit();
+        }
+        ++kc;
+      };
+      int m_tile, n_tile;
+      for (int it = 0; tile_at(it, m_tile, n_tile); ++it) {
+        const int b = m_tile / p.tiles_per_utt, t0 = (m_tile % p.tiles_per_utt) * BM;
+        const uint32_t tacc = tmem_base + half * 128 + lane_off;
+        const float* sbias_h = s_bias + half * 128;
+        mbar_wait(acc_full, it & 1);
+        tc_fence_after();
+        float mean = 0.f, rstd = 1.f;
+        if (LN) {
+          float sum = 0.f, sq = 0.f;
+          for_chunks4(tacc, [&](int k, const uint32_t (&r)[32]) {
+            const float4* sb = reinterpret_cast<const float4*>(sbias_h + k * 32);
+            float s4[4] = {0.f, 0.f, 0.f, 0.f}, q4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 b4 = sb[j];
+              const float v0 = __uint_as_float(r[j * 4 + 0]) + b4.x, v1 = __uint_as_float(r[j * 4 + 1]) + b4.y;
+              const float v2 = __uint_as_float(r[j * 4 + 2]) + b4.z, v3 = __uint_as_float(r[j * 4 + 3]) + b4.w;
+              s4[0] += v0; s4[1] += v1; s4[2] += v2; s4[3] += v3;
+              q4[0] = fmaf(v0, v0, q4[0]); q4[1] = fmaf(v1, v1, q4[1]); q4[2] = fmaf(v2, v2, q4[2]); q4[3] = fmaf(v3, v3, q4[3]);
+            }
+            sum += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+            sq += (q4[0] + q4[1]) + (q4[2] + q4[3]);
+          });
+          float2* st = s_stat + (it & 1) * 256;
+          st[half * 128 + row] = make_float2(sum, sq);
+          named_bar_sync(3, 256);
+          const float2 o = st[(half ^ 1) * 128 + row];
+          sum += o.x; sq += o.y;
+          mean = sum * (1.f / BN);
+          rstd = rsqrtf(fmaxf(sq * (1.f / BN) - mean * mean, 0.f) + 1e-5f);
+        }
+        uint32_t a2[4][16];                          // this thread's 128 first-stage outputs as bf16 pairs
+        for_chunks4(tacc, [&](int k, const uint32_t (&r)[32]) {
+          const int c = half * 4 + k;
+          const float4* sb = reinterpret_cast<const float4*>(sbias_h + k * 32);
+          float v[32];
+          if (LN) {
+            const float4* g4 = reinterpret_cast<const float4*>(s_lng + c * 32);
+            const float4* b4 = reinterpret_cast<const float4*>(s_lnb + c * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 g = g4[j], bb = b4[j], bi = sb[j];
+              v[j * 4 + 0] = (__uint_as_float(r[j * 4 + 0]) + bi.x - mean) * (rstd * g.x) + bb.x;
+              v[j * 4 + 1] = (__uint_as_float(r[j * 4 + 1]) + bi.y - mean) * (rstd * g.y) + bb.y;
+              v[j * 4 + 2] = (__uint_as_float(r[j * 4 + 2]) + bi.z - mean) * (rstd * g.z) + bb.z;
+              v[j * 4 + 3] = (__uint_as_float(r[j * 4 + 3]) + bi.w - mean) * (rstd * g.w) + bb.w;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 b4 = sb[j];
+              v[j * 4 + 0] = __uint_as_float(r[j * 4 + 0]) + b4.x; v[j * 4 + 1] = __uint_as_float(r[j * 4 + 1]) + b4.y;
+              v[j * 4 + 2] = __uint_as_float(r[j * 4 + 2]) + b4.z; v[j * 4 + 3] = __uint_as_float(r[j * 4 + 3]) + b4.w;
+            }
+            if (p.act == ACT_RELU) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) a2[k][j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+          if (p.store1) stage_and_store(&tmO, a2[k], c, t0, b);
+        });
+        // every thread of both halves has read its accumulator columns: the bf16 A operand may overwrite them
+        named_bar_sync(3, 256);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) tmem_st16(tmem_base + half * 64 + k * 16 + lane_off, a2[k]);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_empty);
+
+        // ---- epilogue 2
+        mbar_wait(acc_full + 1, it & 1);
+        tc_fence_after();
+        const int t_row = t0 + row;
+        const int t_pe = p.pe != nullptr ? ((b * p.T + min(t_row, p.T - 1)) % p.pe_period) : 0;
+        for_chunks4(tmem_base + BN + half * 128 + lane_off, [&](int k, const uint32_t (&r)[32]) {
+          const int c = half * 4 + k;
+          if (k == 3) {                              // last read of buffer 1: hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty + 1);
+          }
+          const float4* sb = reinterpret_cast<const float4*>(s_bias2 + c * 32);
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b4 = sb[j];
+            v[j * 4 + 0] = __uint_as_float(r[j * 4 + 0]) + b4.x; v[j * 4 + 1] = __uint_as_float(r[j * 4 + 1]) + b4.y;
+            v[j * 4 + 2] = __uint_as_float(r[j * 4 + 2]) + b4.z; v[j * 4 + 3] = __uint_as_float(r[j * 4 + 3]) + b4.w;
+          }
+          if (p.act2 == ACT_RELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          }
+          if (p.pe != nullptr) {
+            const float4* pr = reinterpret_cast<const float4*>(p.pe + (size_t)t_pe * kD + c * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 q4 = __ldg(pr + j);
+              v[j * 4 + 0] = fmaf(p.alpha, q4.x, v[j * 4 + 0]); v[j * 4 + 1] = fmaf(p.alpha, q4.y, v[j * 4 + 1]);
+              v[j * 4 + 2] = fmaf(p.alpha, q4.z, v[j * 4 + 2]); v[j * 4 + 3] = fmaf(p.alpha, q4.w, v[j * 4 + 3]);
+            }
+          }
+          uint32_t pk[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+          stage_and_store(&tmO2, pk, c, t0, b);
+        });
       }
       if (leader) bulk_wait<0>();
     } else {
@@ -499,14 +680,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 }
 
 // ------------------------------------------------------------------ host side
-template <bool LN, bool WS, bool F32 = false, bool PAIR = false>
+template <bool LN, bool WS, bool F32 = false, bool PAIR = false, bool CHAIN = false>
 static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const CUtensorMap& tmO,
-                           const CUtensorMap& tmR, const Dev& p, cudaStream_t s) {
-  using P = Plan<LN, WS, F32, PAIR>;
+                           const CUtensorMap& tmR, const Dev& p, cudaStream_t s, const CUtensorMap* tmW2p = nullptr,
+                           const CUtensorMap* tmO2p = nullptr) {
+  using P = Plan<LN, WS, F32, PAIR, CHAIN>;
+  const CUtensorMap& tmW2 = tmW2p != nullptr ? *tmW2p : tmW;
+  const CUtensorMap& tmO2 = tmO2p != nullptr ? *tmO2p : tmO;
   static PerDeviceOnce once;
   DevInfo di;
   if (const char* e = device_info(&di)) return e;
-  if (const char* e = ensure_smem(gemm2_kernel<LN, WS, F32, PAIR>, P::TOTAL, once, di.dev, "cudaFuncSetAttribute(gemm2) failed"))
+  if (const char* e = ensure_smem(gemm2_kernel<LN, WS, F32, PAIR, CHAIN>, P::TOTAL, once, di.dev, "cudaFuncSetAttribute(gemm2) failed"))
     return e;
   const int g_sm_count = di.sm_count;
   cudaError_t err;
@@ -514,11 +698,12 @@ static const char* launch2(const CUtensorMap& tmA, const CUtensorMap& tmW, const
     const int units = ((p.m_tiles + 1) / 2) * p.n_tiles;   // list entries: pairs of m-tiles
     int pairs = units < g_sm_count / 2 ? units : g_sm_count / 2;
     if (WS) pairs = (pairs / p.n_tiles) * p.n_tiles;      // every pair owns one n-tile
-    err = launch_pdl_pairs(gemm2_kernel<LN, WS, F32, PAIR>, dim3(2 * pairs), dim3(THREADS), P::TOTAL, s, tmA, tmW, tmO, tmR, p);
+    err = launch_pdl_pairs(gemm2_kernel<LN, WS, F32, PAIR, CHAIN>, dim3(2 * pairs), dim3(THREADS), P::TOTAL, s, tmA, tmW, tmO, tmR,
+                           tmW2, tmO2, p);
   } else {
     int grid = p.total_tiles < g_sm_count ? p.total_tiles : g_sm_count;
     if (WS) grid = (grid / p.n_tiles) * p.n_tiles;        // every CTA owns one n-tile
-    err = launch_pdl(gemm2_kernel<LN, WS, F32, PAIR>, dim3(grid), dim3(THREADS), P::TOTAL, s, tmA, tmW, tmO, tmR, p);
+    err = launch_pdl(gemm2_kernel<LN, WS, F32, PAIR, CHAIN>, dim3(grid), dim3(THREADS), P::TOTAL, s, tmA, tmW, tmO, tmR, tmW2, tmO2, p);
   }
   note_launch();
   return err == cudaSuccess ? nullptr : "gemm2 kernel launch failed";
@@ -549,6 +734,61 @@ bool gemm2_supports(const GemmArgs& a) {
   if (ln && (a.N != BN || a.pe != nullptr || a.act != ACT_NONE)) return false;
   if (ln && (a.ld_res % 8 != 0 || !aligned16(a.residual))) return false;
   return true;
+}
+
+// Chained plan: out2 = epi2( epi1(A W^T) W2^T ); N = K2 = 256, K1 <= 256, one tap, CTA pairs.
+bool gemm2_chain_supports(const GemmArgs& a) {
+  if (a.W2 == nullptr || a.out2 == nullptr || a.bias2 == nullptr) return false;
+  if (a.N != BN || a.taps != 1 || a.kc_per_tap > 4 || a.out_f32 != nullptr || a.out_last != nullptr || a.residual_f32 != nullptr)
+    return false;
+  if ((a.ln_g != nullptr) != (a.residual != nullptr)) return false;
+  if (a.ln_g != nullptr && a.act != ACT_NONE) return false;
+  if (a.act == ACT_TANH || a.act2 == ACT_TANH) return false;
+  if (a.out_bf16 != nullptr && (a.ld_bf16 % 8 != 0 || !aligned16(a.out_bf16))) return false;
+  if (a.ld_out2 % 8 != 0 || !aligned16(a.out2) || !aligned16(a.W2)) return false;
+  if (a.residual != nullptr && (a.ld_res % 8 != 0 || !aligned16(a.residual))) return false;
+  const int m_tiles = a.B * ((a.T + BM - 1) / BM);
+  return m_tiles >= 2;
+}
+
+const char* gemm2_chain_launch(const GemmArgs& a, cudaStream_t s) {
+  Dev p;
+  memset(&p, 0, sizeof(p));
+  p.T = a.T; p.N = a.N;
+  p.tap_off = a.tap_off; p.kc_per_tap = a.kc_per_tap; p.num_kb = a.kc_per_tap;
+  p.tiles_per_utt = (a.T + BM - 1) / BM;
+  p.m_tiles = a.B * p.tiles_per_utt;
+  p.n_tiles = 1; p.total_tiles = p.m_tiles;
+  p.bias = a.bias; p.act = a.act;
+  p.pe = a.pe; p.alpha = a.alpha; p.pe_period = a.pe != nullptr ? a.pe_period : 1;
+  p.ln_g = a.ln_g; p.ln_b = a.ln_b;
+  p.bias2 = a.bias2; p.act2 = a.act2; p.store1 = a.out_bf16 != nullptr;
+  const int ktot = p.num_kb * BK;
+  CUtensorMap tmA, tmW, tmO, tmR, tmW2, tmO2;
+  const char* e = make_tmap_3d(&tmA, a.A, (uint64_t)a.C, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.C * 2,
+                               (uint64_t)a.T * a.C * 2, BK, BM);
+  if (e) return e;
+  e = make_tmap_3d(&tmW, a.W, (uint64_t)ktot, (uint64_t)BN, 1, (uint64_t)ktot * 2, (uint64_t)ktot * 2 * BN, BK, BN / 2);
+  if (e) return e;
+  e = make_tmap_3d(&tmW2, a.W2, (uint64_t)BN, (uint64_t)BN, 1, (uint64_t)BN * 2, (uint64_t)BN * 2 * BN, BK, BN / 2);
+  if (e) return e;
+  e = make_tmap_3d(&tmO2, a.out2, (uint64_t)BN, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_out2 * 2,
+                   (uint64_t)a.T * a.ld_out2 * 2, 32, BM, 64);
+  if (e) return e;
+  if (a.out_bf16 != nullptr) {
+    e = make_tmap_3d(&tmO, a.out_bf16, (uint64_t)BN, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_bf16 * 2,
+                     (uint64_t)a.T * a.ld_bf16 * 2, 32, BM, 64);
+    if (e) return e;
+  } else {
+    tmO = tmO2;
+  }
+  if (a.residual != nullptr) {
+    e = make_tmap_3d(&tmR, a.residual, (uint64_t)BN, (uint64_t)a.T, (uint64_t)a.B, (uint64_t)a.ld_res * 2,
+                     (uint64_t)a.T * a.ld_res * 2, 64, BM);
+    if (e) return e;
+    return launch2<true, true, false, true, true>(tmA, tmW, tmO, tmR, p, s, &tmW2, &tmO2);
+  }
+  return launch2<false, true, false, true, true>(tmA, tmW, tmO, tmO, p, s, &tmW2, &tmO2);
 }
 
 const char* gemm2_launch(const GemmArgs& a, cudaStream_t s) {

@@ -65,11 +65,17 @@ struct GemmArgs {
   bf16* out_bf16; int ld_bf16;            // nullable
   float* out_f32; int ld_f32;             // nullable
   float* out_last;                        // if set, column N-1 goes to out_last[row] instead (stop head)
+  // chained second GEMM (gemm2.cu CHAIN plan; N == 256): out2 = epi2( epi1(...) W2^T ) with epi2 = +bias2, act2,
+  // +alpha*pe (pe / alpha / pe_period then belong to the SECOND epilogue); out_bf16 may be null (first result not stored)
+  const bf16* W2; const float* bias2; int act2;
+  bf16* out2; int ld_out2;
 };
 
 const char* gemm_launch(const GemmArgs& a, cudaStream_t s);   // returns nullptr or an error string
 bool gemm2_supports(const GemmArgs& a);                        // persistent bf16-out kernel (gemm2.cu)
 const char* gemm2_launch(const GemmArgs& a, cudaStream_t s);
+bool gemm2_chain_supports(const GemmArgs& a);                  // two chained GEMMs in one launch (CTA pairs, K <= 256)
+const char* gemm2_chain_launch(const GemmArgs& a, cudaStream_t s);
 
 // Fused FFN block: out = LayerNorm(x + W2 relu(W1 x + b1) + b2) over M rows of 256 channels (ffn.cu).
 // x, out bf16 [M][256] (distinct buffers), w1 bf16 [1024][256], w2 bf16 [256][1024], biases / LN fp32.
