@@ -51,7 +51,8 @@ def test_forward_writes_stay_inside_their_buffers(B, Tp, Tm):
     ph, mel, pl, ml = (t.to(DEV) for t in O.make_inputs(B, Tp, Tm, seed=8))
     ws_bytes = lib.tts_workspace_bytes(B, Tp, Tm)
     n = B * Tm
-    A = Arena(ws_bytes + (2 * n * 80 + n + 3 * B * 4 * Tm * Tp) * 4 + 16 * (GUARD + 1024))
+    A = Arena(ws_bytes + (3 * n * 80 + n + 3 * B * 4 * Tm * Tp) * 4 + n * 168 * 2 + lib.tts_loss_scratch_bytes()
+              + 16 * (GUARD + 1024))
     ws, _ = A.take(ws_bytes)
     pre, pre_t = A.take(n * 80 * 4)
     post, post_t = A.take(n * 80 * 4)

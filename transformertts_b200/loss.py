@@ -24,6 +24,7 @@ class TransformerTTSLoss(nn.Module):
         self.register_buffer("pos_weight", torch.tensor(float(stop_weight)))      # loss.py:13
         self._stop_weight = float(stop_weight)
         self._scratch = None
+        self.values = None                     # [total, pred_mel, post_mel, stop] of the last call (device tensor)
 
     def forward(self, outputs: Dict[str, torch.Tensor], mel: torch.Tensor, lengths: torch.Tensor) -> Dict[str, torch.Tensor]:
         lib = _ext.load()
@@ -45,4 +46,5 @@ class TransformerTTSLoss(nn.Module):
             _ext.check(lib.tts_loss(_ext.ptr(pred), _ext.ptr(post), _ext.ptr(stop), _ext.ptr(mel), _ext.ptr(lengths), B, T,
                                     self._stop_weight, _ext.ptr(out), _ext.ptr(self._scratch), self._scratch.numel() * 8,
                                     C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)), "tts_loss")
+        self.values = out                      # the four scalars as one tensor: one copy brings them all to the host
         return {"total": out[0], "pred_mel": out[1], "post_mel": out[2], "stop": out[3]}   # loss.py:49-54
