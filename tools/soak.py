@@ -52,9 +52,13 @@ for i in range(iters):
     if i % 25 == 24:
         Bi = rng.choice([1, 4, 32])
         iph, _, ipl, _ = make_batch(Bi, rng.randint(20, 150), 8, seed + i)
-        r1 = m.inference(iph.cuda(), ipl.cuda(), max_len=rng.randint(40, 200))
+        ml_ = rng.randint(40, 200)
+        r1 = m.inference(iph.cuda(), ipl.cuda(), max_len=ml_)
+        r2 = m.inference(iph.cuda(), ipl.cuda(), max_len=ml_)
         torch.cuda.synchronize()
         assert torch.isfinite(r1["pred_melspec"]).all()
+        for k in r1:
+            assert torch.equal(r1[k], r2[k]), f"iteration {i}: AR decode {k} of two runs differs (B={Bi})"
     if i % 20 == 19:
         print(f"{i + 1} iterations, {time.time() - t0:.0f} s", flush=True)
 print(f"soak ok: {iters} iterations in {time.time() - t0:.0f} s")
