@@ -490,7 +490,7 @@ def run_ours(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    n0 = lib.tts_launch_count()
+    n0 = lib.tts_launch_count() + model.graph_launches
     step_ms = []
     for _ in range(args.steps):
         flush()                                        # L2 flush between timed iterations (outside the events)
@@ -500,7 +500,7 @@ def run_ours(args):
         b.record()
         b.synchronize()
         step_ms.append(a.elapsed_time(b))
-    launches = int(lib.tts_launch_count() - n0)
+    launches = int(lib.tts_launch_count() + model.graph_launches - n0)   # stream launches + kernels run by graph replays
     barrier()
     ms_step = max_over_ranks(sum(step_ms) / len(step_ms))
     total_valid = sum_over_ranks(valid)

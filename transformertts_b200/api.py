@@ -129,6 +129,7 @@ class TransformerTTS(nn.Module):
         self.serial_encoder = False   # True: keep the encoder branch on the caller's stream (no side stream)
         self.use_cuda_graph = False   # True: replay the forward as a CUDA graph (static output buffers; _forward_graph)
         self._graphs = {}
+        self.graph_launches = 0       # kernel launches executed by graph replays (tts_launch_count sees only captures)
         self.strict_lens = False      # True: reproduce the reference's Tp == max(lens) assert (costs a host sync)
         for key, t in _reference_layout_init(n_phon).items():
             self._register(key, t.to(self.device))
@@ -267,11 +268,13 @@ class TransformerTTS(nn.Module):
             self._forward_launch(lib, args, B, Tp, Tm, flags, return_alignments)    # warm-up outside the capture
             torch.cuda.current_stream(self.device).synchronize()
             g = torch.cuda.CUDAGraph()
+            n0 = lib.tts_launch_count()
             with torch.cuda.graph(g):
                 out = self._forward_launch(lib, args, B, Tp, Tm, flags, return_alignments)
-            hit = (g, out, args, w)                          # keep the inputs / weights of the capture alive
+            hit = (g, out, args, w, int(lib.tts_launch_count() - n0))    # keep the inputs / weights of the capture alive
             self._graphs[key] = hit
         hit[0].replay()
+        self.graph_launches += hit[4]                        # kernels of this library executed through graph replays
         out = hit[1]
         return {"pred_melspec": out["pred_melspec"], "post_melspec": out["post_melspec"], "pred_stop": out["pred_stop"],
                 "alignments": list(out["alignments"])}
