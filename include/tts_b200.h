@@ -15,6 +15,7 @@
  *   tts_postnet          PostNet + residual                     model/model.py:129-135, 310, 388
  *   tts_teacher_forcing_mix   block_mask + apply_teacher_forcing  utils/util.py:103-120
  *   tts_loss             TransformerTTSLoss.forward              loss.py:15-55
+ *   tts_loss_static      (no reference counterpart) tts_loss over scratch built into the library: allocates nothing
  *   tts_pack_outputs     (no reference counterpart) pred/post/stop -> one bf16 buffer for a single D2H copy
  *   tts_op_linear / tts_op_linear_chain / tts_op_conv1d / tts_op_attention / tts_op_ffn
  *                        the torch.nn operators underneath (model/module.py:4-53,
@@ -152,6 +153,22 @@ size_t tts_loss_scratch_bytes(void);
  * pred/post/mel f32 [B][T][80], stop f32 [B][T].  Deterministic (fixed reduction order). */
 int tts_loss(const float* pred, const float* post, const float* stop, const float* mel, const int64_t* mel_lens, int B,
              int T, float pos_weight, float* out4, void* scratch, size_t scratch_bytes, void* stream);
+
+/* tts_loss without caller scratch and without any device allocation.  (No counterpart in the reference: it exists for
+ * hosts that embed this library where device memory may not be allocated -- a plugin inside a framework that owns and
+ * budgets the memory pool, a latency-critical serving thread that cannot take cudaMalloc's device-wide synchronisation,
+ * a process whose HBM is already fully reserved by a caching allocator.)  Same arguments, same kernels and bit-identical
+ * out4 as tts_loss; the per-block partial sums go to a fixed 24 KiB array inside the library (1024 partials of 24 bytes,
+ * enough for 4 blocks per SM on devices of up to 256 SMs; each GPU that loads the library holds it until the process
+ * exits).  A device that needs more partials is refused with an error -- use tts_loss there.  Calls cudaMalloc,
+ * cudaFree or an allocating library routine never.
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device current)
+ * and caches it; make that first call outside any stream capture.  All calls on a device share the array and it keeps
+ * the previous call's partial sums (every launch overwrites the slots it then reads, so nothing needs clearing): calls
+ * whose kernels may overlap on the GPU -- two streams, two host threads -- race on it and must be serialised by the
+ * caller. */
+int tts_loss_static(const float* pred, const float* post, const float* stop, const float* mel, const int64_t* mel_lens,
+                    int B, int T, float pos_weight, float* out4, void* stream);
 
 /* pred / post f32 [rows][80] + stop f32 [rows] -> packed bf16 [rows][168] (cols 0-79 pred, 80-159 post, 160 stop,
  * 161-167 zero): one buffer, one device -> host copy per step at half the bytes. */

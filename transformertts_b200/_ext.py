@@ -65,6 +65,7 @@ SIGNATURES = {
     "tts_teacher_forcing_mix": (C.c_int, [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]),
     "tts_loss_scratch_bytes": (C.c_size_t, []),
     "tts_loss": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp, vp, C.c_size_t, vp]),
+    "tts_loss_static": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp, vp]),
     "tts_pack_outputs": (C.c_int, [vp, vp, vp, C.c_longlong, vp, vp]),
     "tts_op_linear": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_int, vp, vp, vp,
                                 vp, vp, vp]),

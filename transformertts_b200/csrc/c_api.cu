@@ -622,6 +622,19 @@ extern "C" int tts_loss(const float* pred, const float* post, const float* stop,
   return 0;
 }
 
+// Variant of tts_loss for callers that cannot allocate device memory: the partial sums go to a fixed array inside the
+// library (train_aux.cu) instead of caller scratch.  No cudaMalloc / cudaFree here or below.
+extern "C" int tts_loss_static(const float* pred, const float* post, const float* stop, const float* mel,
+                               const int64_t* mel_lens, int B, int T, float pos_weight, float* out4, void* stream) {
+  if (pred == nullptr || post == nullptr || stop == nullptr || mel == nullptr || mel_lens == nullptr || out4 == nullptr)
+    return fail("tts_loss_static: NULL pointer");
+  if (B <= 0 || T <= 0) return fail("tts_loss_static: B and T must be positive");
+  if (((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(post) | reinterpret_cast<uintptr_t>(mel)) & 15) != 0)
+    return fail("tts_loss_static: tensors must be 16-byte aligned");
+  TRY(loss_static_launch(pred, post, stop, mel, mel_lens, B, T, pos_weight, out4, (cudaStream_t)stream));
+  return 0;
+}
+
 extern "C" int tts_pack_outputs(const float* pred, const float* post, const float* stop, long long rows, void* packed,
                                 void* stream) {
   if (pred == nullptr || post == nullptr || stop == nullptr || packed == nullptr) return fail("tts_pack_outputs: NULL pointer");

@@ -121,6 +121,9 @@ const char* tf_mix_launch(const float* pred, const float* mel, const uint8_t* se
 int loss_blocks(int sm_count);                                 // partial sums the loss keeps in its scratch (24 B each)
 const char* loss_launch(const float* pred, const float* post, const float* stop, const float* mel, const int64_t* lens,
                         int B, int T, float pos_weight, float* out4, void* scratch, size_t scratch_bytes, cudaStream_t s);
+// same two kernels over a scratch array that is part of the library image (no caller scratch, nothing allocated)
+const char* loss_static_launch(const float* pred, const float* post, const float* stop, const float* mel,
+                               const int64_t* lens, int B, int T, float pos_weight, float* out4, cudaStream_t s);
 const char* pack_out_launch(const float* pred, const float* post, const float* stop, long long rows, void* out,
                             cudaStream_t s);
 

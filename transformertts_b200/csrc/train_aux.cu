@@ -6,6 +6,8 @@
 // All three are HBM-bound streaming kernels: 16-byte coalesced loads, padded rows skipped (their bytes are never
 // read), grids sized in multiples of the SM count.  The loss is reduced in two deterministic stages (per-block fp64
 // partials in a caller-owned scratch, then one block in fixed order), so a loss value is bit-reproducible.
+#include <mutex>
+
 #include "kernels.h"
 
 namespace tts {
@@ -123,6 +125,56 @@ const char* loss_launch(const float* pred, const float* post, const float* stop,
   const int blocks = loss_blocks(di.sm_count);
   if (scratch == nullptr || scratch_bytes < sizeof(LossPartial) * (size_t)blocks) return "loss: scratch too small";
   LossPartial* part = reinterpret_cast<LossPartial*>(scratch);
+  loss_partial_kernel<<<blocks, AUX_THREADS, 0, s>>>(reinterpret_cast<const float4*>(pred),
+                                                     reinterpret_cast<const float4*>(post), stop,
+                                                     reinterpret_cast<const float4*>(mel), lens, B, T, pos_weight, part);
+  loss_final_kernel<<<1, 32, 0, s>>>(part, blocks, lens, B, T, out4);
+  note_launch(2);
+  return cudaGetLastError() == cudaSuccess ? nullptr : "loss kernel launch failed";
+}
+
+// ------------------------------------------------------------------ loss with library-owned scratch (tts_loss_static)
+// Some callers of this library are not allowed to allocate device memory at the point where they want a loss value:
+// a plugin running inside a host framework whose memory pool is owned and budgeted by someone else, a real-time or
+// serving thread where cudaMalloc's implicit device synchronisation is unacceptable, a process that has handed every
+// free byte of HBM to a caching allocator and would fail a late cudaMalloc.  For them the stage-1 partial sums live in
+// the array below, which is part of the library image: every GPU that loads libtts_b200.so carries these 24 KiB from
+// module load until the process exits, and nothing is allocated or freed per call.
+//
+// kLossStaticPartials bounds the stage-1 grid (4 blocks per SM, as in loss_launch, so both entry points add the same
+// numbers in the same order): 1024 partials cover devices of up to 256 SMs.  A device that would need more is refused.
+// Nothing in the array has to start at zero: each stage-1 block overwrites its own slot and stage 2 reads exactly the
+// slots that were just written.  The array is shared by every call on a device and keeps the previous call's partials,
+// so two calls whose kernels can overlap on the GPU (different streams, different host threads) race on it.
+constexpr int kLossStaticPartials = 1024;
+static __device__ __align__(256) LossPartial g_loss_static[kLossStaticPartials];
+
+// In host code `g_loss_static` is only a handle for the runtime, not a device address; the address a kernel can use is
+// looked up once per device (with that device current) and cached here.
+static std::mutex g_loss_static_mu;
+static LossPartial* g_loss_static_ptr[kMaxDevices] = {};
+
+const char* loss_static_launch(const float* pred, const float* post, const float* stop, const float* mel,
+                               const int64_t* lens, int B, int T, float pos_weight, float* out4, cudaStream_t s) {
+  DevInfo di;
+  if (const char* e = device_info(&di)) return e;
+  const int blocks = loss_blocks(di.sm_count);
+  if (blocks > kLossStaticPartials)
+    return "tts_loss_static: this device needs more than the 1024 partial sums (256 SMs) the built-in scratch holds; "
+           "use tts_loss with caller-provided scratch";
+  LossPartial* part = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_loss_static_mu);
+    part = g_loss_static_ptr[di.dev];
+    if (part == nullptr) {                                          // first call on this device: resolve the symbol
+      void* p = nullptr;
+      if (cudaGetSymbolAddress(&p, g_loss_static) != cudaSuccess || p == nullptr) {
+        (void)cudaGetLastError();
+        return "tts_loss_static: cudaGetSymbolAddress failed for the built-in scratch";
+      }
+      part = g_loss_static_ptr[di.dev] = static_cast<LossPartial*>(p);
+    }
+  }
   loss_partial_kernel<<<blocks, AUX_THREADS, 0, s>>>(reinterpret_cast<const float4*>(pred),
                                                      reinterpret_cast<const float4*>(post), stop,
                                                      reinterpret_cast<const float4*>(mel), lens, B, T, pos_weight, part);
