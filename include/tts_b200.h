@@ -188,8 +188,9 @@ int tts_op_linear(const void* A, const void* W, const float* bias, int M, int N,
  *   y1 = LayerNorm(residual + A W1^T + b1) when ln_g != NULL (act1 must be 0), else act1(A W1^T + b1);
  *   out2 = act2(y1_bf16 W2^T + b2) + alpha * pe[row % pe_period]   (pe may be NULL).
  * y1 stays on the SM (bf16, tensor memory) as the A operand of the second GEMM; it is also stored to out1_bf16 unless
- * that is NULL.  This is how tts_forward runs out-projection + LayerNorm -> cross-attention Q projection and
- * prenet 1 -> prenet 2 + PE. */
+ * that is NULL.  tts_forward runs out-projection + LayerNorm -> cross-attention Q projection and prenet 1 -> prenet 2 + PE
+ * this way only when the process sets TTS_GEMM_CHAIN=1; by default it launches the two GEMMs separately (measured
+ * faster inside the whole forward, profiles/r02_gemm_chain_ab.txt). */
 int tts_op_linear_chain(const void* A, const void* W1, const float* b1, int M, int K1, int act1, const void* residual,
                         const float* ln_g, const float* ln_b, const void* W2, const float* b2, int act2,
                         const float* pe, float alpha, int pe_period, void* out1_bf16, void* out2_bf16, void* stream);

@@ -97,6 +97,21 @@ def test_loss_matches_oracle(B, T, w):
         assert float(a[k]) == float(b[k])             # deterministic reduction order
 
 
+def test_loss_uses_the_pos_weight_buffer_after_load_state_dict():
+    from transformertts_b200 import TransformerTTSLoss
+    g = torch.Generator().manual_seed(11)
+    B, T = 4, 60
+    lens = torch.randint(30, T + 1, (B,), generator=g)
+    mel = torch.randn(B, T, 80, generator=g)
+    out = {"pred_melspec": mel + 0.5, "post_melspec": mel - 0.25, "pred_stop": 4 * torch.randn(B, T, generator=g)}
+    crit = TransformerTTSLoss(stop_weight=8.0).to(DEV)
+    crit.load_state_dict({"pos_weight": torch.tensor(2.5)})
+    ref = TO.loss({k: v.double() for k, v in out.items()}, mel.double(), lens, 2.5)
+    got = crit({k: v.to(DEV) for k, v in out.items()}, mel.to(DEV), lens.to(DEV))
+    for k in ref:
+        np.testing.assert_allclose(float(got[k]), float(ref[k]), rtol=LOSS_RTOL)
+
+
 # ------------------------------------------------------------------ bf16 mel input, packed outputs, feeder / fetcher
 def _model(sd):
     from transformertts_b200 import TransformerTTS

@@ -106,3 +106,17 @@ def test_gpu_only_entry_points_fail_loudly_on_cpu_tensors():
         TransformerTTSLoss()({"pred_melspec": x, "post_melspec": x, "pred_stop": torch.zeros(1, 4)}, x, torch.tensor([4]))
     with pytest.raises(RuntimeError, match="GPU only"):
         apply_teacher_forcing(x, x, torch.tensor([4]), 0.5)
+
+
+def test_loss_pos_weight_follows_the_registered_buffer():
+    """loss.py:13,44: the reference reads the `pos_weight` buffer, so a checkpointed or edited value must win over the
+    constructor argument."""
+    from transformertts_b200 import TransformerTTSLoss
+    crit = TransformerTTSLoss(stop_weight=8.0)
+    assert crit._weight() == 8.0
+    crit.load_state_dict({"pos_weight": torch.tensor(3.0)})
+    assert crit._weight() == 3.0
+    crit.pos_weight.fill_(5.0)
+    assert crit._weight() == 5.0
+    crit.pos_weight = torch.tensor(2.0)
+    assert crit._weight() == 2.0

@@ -15,7 +15,7 @@ SOURCES = ["host.cu", "gemm2.cu", "ffn.cu", "attention2.cu", "attention3.cu", "d
 HEADERS = ["ptx.cuh", "kernels.h", "decode.cuh", os.path.join("..", "..", "include", "tts_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math" if os.environ.get("TTS_FAST_MATH") else "-DTTS_EXACT_MATH"]
-NVCC_FLAGS += os.environ.get("TTS_EXTRA_NVCC_FLAGS", "").split()      # e.g. tools/sanitize.sh: a longer wait bound
+NVCC_FLAGS += os.environ.get("TTS_EXTRA_NVCC_FLAGS", "").split()      # e.g. -DTTS_... switches for A/B builds
 
 
 def _nvcc():

@@ -409,7 +409,8 @@ static const char* run_decoder(const TtsWeights* w, const void* mel, int flags, 
     // decoder prenet on the go-frame-shifted target (model/model.py:278-279, 297): frame t reads mel[t-1]
     GemmArgs g = conv_args(mel16, nb, Tm, kMel, w->pre1_w, w->pre1_b, kD, 1, -1);
     g.act = ACT_RELU;
-    // prenet 1 -> prenet 2 + PE chained in one launch (the hidden activation stays in tensor memory)
+    // prenet 1 -> prenet 2 + PE: two launches by default; one chained launch (hidden activation stays in tensor memory)
+    // only with TTS_GEMM_CHAIN=1
     g.W2 = (const bf16*)w->pre2_w; g.bias2 = w->pre2_b; g.act2 = ACT_RELU;
     g.pe = w->pe; g.alpha = w->alpha; g.pe_period = Tm;
     g.out2 = d1; g.ld_out2 = kD;
@@ -433,7 +434,7 @@ static const char* run_decoder(const TtsWeights* w, const void* mel, int flags, 
     const TtsDecLayerW& L = w->dec[l];
     if ((e = proj(x, Nm, kD, L.sa.w_in, L.sa.b_in, 3 * kD, ACT_NONE, qkv, s))) return e;
     if ((e = run_attention(qkv, 3 * kD, qkv + kD, qkv + 2 * kD, 3 * kD, att, nullptr, mel_len, nb, Tm, Tm, 1, s))) return e;
-    {                                                // y = LN1(x + att Wo^T + b), cq = y Wq^T + bq: one chained launch
+    {                                                // y = LN1(x + att Wo^T + b), cq = y Wq^T + bq (chained launch: opt-in)
       GemmArgs g = linear_args(att, Nm, kD, L.sa.w_out, L.sa.b_out, kD);
       g.residual = x; g.ld_res = kD;
       g.ln_g = L.ln1.g; g.ln_b = L.ln1.b;

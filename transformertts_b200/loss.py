@@ -22,9 +22,19 @@ class TransformerTTSLoss(nn.Module):
     def __init__(self, stop_weight: float = 8.0):
         super().__init__()
         self.register_buffer("pos_weight", torch.tensor(float(stop_weight)))      # loss.py:13
-        self._stop_weight = float(stop_weight)
+        self._stop_weight = float(stop_weight)  # host copy of the buffer, refreshed when the buffer changes (_weight())
+        self._pw_seen = (self.pos_weight, self.pos_weight._version)
         self._scratch = None
         self.values = None                     # [total, pred_mel, post_mel, stop] of the last call (device tensor)
+
+    def _weight(self) -> float:
+        """pos_weight as the reference uses it (the registered buffer, loss.py:13,44): a value restored by
+        load_state_dict, replaced by .to() or edited in place is picked up; the device -> host read happens only then."""
+        pw = self.pos_weight
+        if self._pw_seen[0] is not pw or self._pw_seen[1] != pw._version:
+            self._stop_weight = float(pw)
+            self._pw_seen = (pw, pw._version)
+        return self._stop_weight
 
     def forward(self, outputs: Dict[str, torch.Tensor], mel: torch.Tensor, lengths: torch.Tensor) -> Dict[str, torch.Tensor]:
         lib = _ext.load()
@@ -44,7 +54,7 @@ class TransformerTTSLoss(nn.Module):
                 self._scratch = torch.empty((need + 7) // 8, dtype=torch.float64, device=dev)
             out = torch.empty(4, dtype=torch.float32, device=dev)
             _ext.check(lib.tts_loss(_ext.ptr(pred), _ext.ptr(post), _ext.ptr(stop), _ext.ptr(mel), _ext.ptr(lengths), B, T,
-                                    self._stop_weight, _ext.ptr(out), _ext.ptr(self._scratch), self._scratch.numel() * 8,
+                                    self._weight(), _ext.ptr(out), _ext.ptr(self._scratch), self._scratch.numel() * 8,
                                     C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)), "tts_loss")
         self.values = out                      # the four scalars as one tensor: one copy brings them all to the host
         return {"total": out[0], "pred_mel": out[1], "post_mel": out[2], "stop": out[3]}   # loss.py:49-54
