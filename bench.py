@@ -175,24 +175,32 @@ def cpu_baselines(reps=3, ar_frames=200):
 
 
 def our_config(world):
-    """`config` of the JSON line; the reference arm prints the same object (same workload, metric and unit)."""
-    c = {"workload": "configs[1]: teacher-forced forward, B=64 per GPU, Tp=150, Tm=800, alignments "
-                     "returned (3x[B,4,Tm,Tp] fp32)",
-         "batch_per_gpu": CFG2["B"], "parallelism": f"batch-sharded x{world}, no collective",
-         "l2": "256 MiB buffer written between timed iterations; working set (475 MB) also exceeds L2",
-         "launch": "forward replayed as a CUDA graph (module option use_cuda_graph; --no-graph for stream launches)",
-         "weights": "random init (reference init laws), bf16 on the GPU arm / fp32 on the CPU arm"}
-    return c
+    """`config` of the JSON line: the workload only, so both arms print the same object truthfully; how each arm runs it
+    (graph replay, L2 flush, weight precision) is in that arm's `run` object."""
+    return {"workload": "configs[1]: teacher-forced forward, B=64 per GPU, Tp=150, Tm=800, alignments "
+                        "returned (3x[B,4,Tm,Tp] fp32)",
+            "batch_per_gpu": CFG2["B"], "parallelism": f"batch-sharded x{world}, no collective",
+            "l2": "GPU arm: 256 MiB buffer written between timed iterations, and the working set (475 MB) exceeds L2; "
+                  "CPU arm: n/a"}
+
+
+def run_notes(arm, graph=True):
+    if arm == "reference":
+        return {"launch": "reference model.TransformerTTS.forward under torch.no_grad(), eval mode, CPU threads",
+                "weights": "random init (reference init laws), fp32"}
+    return {"launch": ("forward replayed as a CUDA graph (module option use_cuda_graph)" if graph else
+                       "stream launches (--no-graph)"),
+            "weights": "random init (reference init laws), bf16 on the GPU arm"}
 
 
 def run_reference(args):
     """--impl reference: the reference's own CPU implementation, same metric / unit / config; one step = one forward over
-    a bounded sample of the workload (configs[0]: 16 utterances of the same lens law)."""
+    configs[1] itself (B=64, Tp=150, Tm=800: the batch rank 0 of the GPU arm runs), about 1-2 s per step on 16 cores."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     ref = CpuReference()
-    ph, mel, pl, ml = make_batch(CFG1["B"], CFG1["Tp"], CFG1["Tm"], seed=1)
+    ph, mel, pl, ml = make_batch(CFG2["B"], CFG2["Tp"], CFG2["Tm"], seed=1)
     frames = int(ml.sum())
     times = []
     for _ in range(max(args.warmup, 1)):
@@ -203,15 +211,15 @@ def run_reference(args):
         times.append(time.perf_counter() - t0)
     ms = 1e3 * sum(times) / len(times)
     value = frames / (ms / 1e3)
-    sample = (f"each step: configs[0] exactly (B=16, Tp=150, Tm=800; {frames} valid frames), i.e. 16 utterances of the "
-              f"64-utterance workload; {ref.describe()}, torch.set_num_threads({ref.threads})")
+    sample = (f"each step: configs[1] exactly (B=64, Tp=150, Tm=800; {frames} valid frames, the batch of the GPU arm's "
+              f"rank 0), alignments returned; {ref.describe()}, torch.set_num_threads({ref.threads})")
     line = {
         "impl": "reference", "metric": "mel frames/sec (teacher-forced forward)", "value": value,
         "unit": "valid mel frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": our_config(1),
-        "frames": {"batch": CFG1["B"], "valid_frames_per_step": frames, "padded_frames_per_step": CFG1["B"] * CFG1["Tm"]},
+        "config": our_config(1), "run": run_notes("reference"),
+        "frames": {"batch": CFG2["B"], "valid_frames_per_step": frames, "padded_frames_per_step": CFG2["B"] * CFG2["Tm"]},
         "cpu_baseline": {"value": value, "unit": "valid mel frames/s", "cores": ref.threads, "kind": ref.kind,
                          "sample": sample},
         "e2e": {"value": value, "unit": "valid mel frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -484,6 +492,11 @@ def run_ours(args):
     # ---- device-resident forward: the headline `value`.  The module replays the forward as a CUDA graph
     # (TransformerTTS.use_cuda_graph: ~50 launches on two streams captured once per shape / input buffers)
     model.use_cuda_graph = not args.no_graph
+    if model.use_cuda_graph:                           # inputs resident in the graph's own static buffers: no per-step copy
+        gin = model.graph_input_buffers(B, Tp, Tm)
+        for dst, src in zip(gin, (dph, dmel, dpl, dml)):
+            dst.copy_(src)
+        dph, dmel, dpl, dml = gin
     for _ in range(max(args.warmup, 3)):
         out = model(dph, dmel, dpl, dml)
     barrier()
@@ -565,11 +578,48 @@ def run_ours(args):
         return {"value": total_valid / sec, "ms_per_step": sec * 1e3, "h2d_bytes_per_step": bytes_io[0],
                 "d2h_bytes_per_step": bytes_io[1], "runs_ms_per_step": [x * 1e3 for x in runs]}
 
+    def e2e_validation_step(host_batch):
+        """harness.LightningModule.validation_step (the statement-by-statement stand-in of lightning_module.py:102-130)
+        driven as Trainer.validate drives it: PinnedFeeder -> prepare_batch -> forward (graph replay) -> criterion ->
+        loss['total'].item() EVERY step (a host sync per step, as in the reference)."""
+        from transformertts_b200.harness import LightningModule
+        cfg = {"model": {}, "loss": {"stop_weight": 8.0}, "training": {"num_epochs": 300, "teacher_forcing_mode": "linear",
+                                                                       "log_interval": 10 ** 9}}
+        lm = LightningModule.__new__(LightningModule)    # the module under test is the bench's model, not a fresh one
+        lm.device, lm.model, lm.criterion, lm.config, lm.exp_dir = dev, model, crit, cfg, None
+        lm.train_losses, lm.valid_losses, lm.example_batch, lm.log_interval = [], [], None, 10 ** 9
+        lm.current_epoch, lm.total_train_batches, lm.total_valid_batches = 0, 0, 0
+        lm.plots, lm.log_fn, lm.logged = {}, None, {}
+        feeder = PinnedFeeder((), dev)
+
+        def run(n):
+            model.use_cuda_graph = not args.no_graph
+            feeder.batches = (host_batch for _ in range(n))
+            lm.valid_losses.clear()
+            for i, b in enumerate(feeder):
+                lm.validation_step(b, i + 1)              # batch_idx >= 1: the plots of batch 0 are UI, out of scope
+            torch.cuda.synchronize()
+            return sum(lm.valid_losses) / len(lm.valid_losses)
+
+        run(3)
+        runs = []
+        for _ in range(3):
+            barrier()
+            t0 = time.perf_counter()
+            mean_loss = run(args.steps)
+            runs.append((time.perf_counter() - t0) / args.steps)
+        barrier()
+        sec = max_over_ranks(sorted(runs)[1])
+        return {"value": total_valid / sec, "ms_per_step": sec * 1e3, "h2d_bytes_per_step": feeder.h2d_bytes,
+                "d2h_bytes_per_step": 4, "runs_ms_per_step": [x * 1e3 for x in runs], "mean_total_loss": mean_loss}
+
     # headline: the reference's own step around forward -- LightningModule.validation_step (lightning_module.py:102-130):
     # batch to the device, forward, criterion on the device, the loss scalars back to the host (`.item()`); the outputs
     # and alignments stay on the device (utils/plot.py pulls single maps once per epoch)
-    e2e_main = e2e_variant(host_f32, loss_only=True)
-    e2e_variants = {"outputs_f32_d2h": e2e_variant(host_b16, check=True)}     # round-1 definition: pred | post | stop to the host
+    e2e_main = e2e_validation_step(host_f32)
+    e2e_outputs = e2e_variant(host_b16, check=True)      # round-1 definition: pred | post | stop to the host every step
+    e2e_variants = {"outputs_f32_d2h": e2e_outputs,
+                    "loss_scalars_async": e2e_variant(host_f32, loss_only=True)}   # no per-step host sync (r02's headline)
     if not args.no_extra:
         e2e_variants.update({
             "outputs_f32_d2h_f32_mel_in": e2e_variant(host_f32, check=True),
@@ -762,18 +812,20 @@ def run_ours(args):
             "metric": "mel frames/sec (teacher-forced forward)", "value": value, "unit": "valid mel frames/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": our_config(world),
+            "config": our_config(world), "run": run_notes("ours", graph=not args.no_graph),
             "frames": {"valid_frames_per_step": total_valid, "padded_frames_per_step": total_padded,
                        "padded_frames_per_s": total_padded / (ms_step / 1e3)},
             "e2e": dict(e2e_main, unit="valid mel frames/s",
-                        note="median of 3 runs of K steps of the reference's validation step (lightning_module.py:102-130) "
-                             "through the package's public API: every step a collated pinned host batch (fp32 mel) -> device on "
-                             "a copy stream (transformertts_b200.data.PinnedFeeder, double-buffered), TransformerTTS.forward "
-                             "with alignments, TransformerTTSLoss on the device, the four loss scalars -> pinned host; the "
-                             "outputs stay on the device as in the reference.  e2e_variants.outputs_f32_d2h is the round-1 "
-                             "definition (pred | post | stop fp32 copied to the host every step, one copy, checked bit-equal "
-                             "against the device-resident run); the other variants change the bytes that travel; "
-                             "copy_only_probe runs the same copies without the forward (the host-side limit at N = 8)"),
+                        note="median of 3 runs of K steps of transformertts_b200.harness.LightningModule.validation_step "
+                             "(lightning_module.py:102-130) as Trainer.validate drives it: every step a collated pinned host "
+                             "batch (fp32 mel) -> device on a copy stream (data.PinnedFeeder, double-buffered), "
+                             "TransformerTTS.forward with alignments (graph replay), TransformerTTSLoss on the device, "
+                             "loss['total'].item() -- one host sync per step, as in the reference; outputs stay on the device. "
+                             "e2e_outputs_to_host is the other first-class definition (pred | post | stop fp32 copied to the host "
+                             "every step, checked bit-equal against the device-resident run): it is host-copy bound at N = 8. "
+                             "e2e_variants.loss_scalars_async is round 2's headline (no per-step sync); copy_only_probe runs "
+                             "the copies without the forward"),
+            "e2e_outputs_to_host": dict(e2e_outputs, unit="valid mel frames/s"),
             "e2e_variants": e2e_variants, "cfg1_b16": cfg1,
             "gpu_launches": launches,
             "roofline": roofline, "kernels": kernels, "step_roofline": step_roofline,

@@ -17,6 +17,7 @@ import torch
 
 import tts_oracle as O
 from parity_common import DEV, report
+from transformertts_b200 import _ext
 
 pytestmark = pytest.mark.gpu
 
@@ -118,11 +119,13 @@ def test_forward_side_stream_matches_serial():
 
 
 def test_forward_cuda_graph_mode_matches_stream_launches():
-    """`use_cuda_graph`: the forward replayed as a CUDA graph must give the stream-launched result bit for bit, read new
-    input CONTENTS from the same buffers on every replay, and build a second graph for other buffers / shapes."""
+    """`use_cuda_graph`: the forward replayed as a CUDA graph must give the stream-launched result bit for bit whatever
+    tensors the caller passes (the graph owns its input buffers: fresh device tensors, CPU tensors and the static buffers
+    themselves all hit the same graph), one graph entry per shape, and a result must survive the next call."""
     sd = O.make_state_dict(37)
     m = _model(sd)
-    a = [t.to(DEV) for t in O.make_inputs(4, 70, 260, seed=38)]
+    a_host = O.make_inputs(4, 70, 260, seed=38)
+    a = [t.to(DEV) for t in a_host]
     b = [t.to(DEV) for t in O.make_inputs(4, 70, 260, seed=39)]
     c = [t.to(DEV) for t in O.make_inputs(2, 33, 130, seed=40)]
     want = {}
@@ -139,16 +142,59 @@ def test_forward_cuda_graph_mode_matches_stream_launches():
         for x, y in zip(o["alignments"], want[name]["al"]):
             assert torch.equal(x, y)
 
+    lib = _ext.load()
     check(m(*a), "a")
+    n_capture = lib.tts_launch_count()
     check(m(*a), "a")                       # replay
-    for dst, src in zip(a, b):              # same buffers, new contents (same shapes)
+    oa = m(*[t.clone() for t in a])         # fresh tensors every call (a DataLoader): same graph, no re-capture
+    ob = m(*b)                              # other tensors, same shapes: same graph, the other output set
+    check(oa, "a")                          # ... so the previous result is still intact
+    check(ob, "b")
+    check(m(*a_host), "a")                  # CPU tensors are copied straight into the graph's input buffers
+    check(m(*c), "c")                       # other shapes: second entry
+    n_c = lib.tts_launch_count()
+    sin = m.graph_input_buffers(4, 70, 260)
+    for dst, src in zip(sin, b):
         dst.copy_(src)
-    check(m(*a), "b")
-    check(m(*c), "c")                       # other shapes: second graph
-    check(m(*b), "b")                       # other buffers: third graph
-    assert len(m._graphs) == 3
+    check(m(*sin), "b")                     # the static input buffers themselves: no copy
+    assert len(m._graphs) == 2
+    assert lib.tts_launch_count() == n_c and n_c > n_capture   # only the second shape captured anything after the first
     m.use_cuda_graph = False
     check(m(*c), "c")
+
+
+def test_cuda_graph_outputs_survive_a_fetch_on_another_stream():
+    """OutputFetcher copies outputs to the host on its own stream while the next forward runs.  With graph
+    replay the outputs are static buffers; the replay that reuses an output set must wait for the copy that reads it.
+    Worst case on purpose: ONE output set and the 14 MB alignment maps in the copy, so the copy of step i is still running
+    when step i+1 is issued.  Eight steps of rotating contents, the fetched results checked against stream launches."""
+    from transformertts_b200.data import OutputFetcher
+    sd = O.make_state_dict(41)
+    m = _model(sd)
+    xs = [[t.to(DEV) for t in O.make_inputs(8, 90, 400, seed=50 + i)] for i in range(3)]
+    want = []
+    for x in xs:
+        o = m(*x)
+        w = {k: o[k].cpu() for k in ("pred_melspec", "post_melspec", "pred_stop")}
+        w["alignments"] = [a.cpu() for a in o["alignments"]]
+        want.append(w)
+    for sets, dtype, with_align in ((1, torch.float32, True), (2, torch.float32, False), (1, torch.bfloat16, False)):
+        m._drop_graphs()
+        m.graph_output_sets = sets
+        m.use_cuda_graph = True
+        fetch = OutputFetcher(DEV, depth=4, dtype=dtype, with_alignments=with_align)
+        got = [fetch(m(*xs[i % 3])) for i in range(8)]
+        fetch.wait()
+        torch.cuda.synchronize()
+        m.use_cuda_graph = False
+        for i in range(4, 8):                              # the four slots the fetcher still holds
+            for k in ("pred_melspec", "post_melspec", "pred_stop"):
+                ref = want[i % 3][k] if dtype == torch.float32 else want[i % 3][k].to(torch.bfloat16)
+                assert torch.equal(got[i][k].reshape(ref.shape), ref), (sets, dtype, i, k)
+            if with_align:
+                for x, y in zip(got[i]["alignments"], want[i % 3]["alignments"]):
+                    assert torch.equal(x, y), (sets, i)
+    m.graph_output_sets = 2
 
 
 def test_forward_rejects_training_mode_and_bad_config():

@@ -21,6 +21,27 @@ from .weights import D, FFN, KS, MAX_PE, N_MELS, PackedWeights
 FLAG_WANT_ALIGN, FLAG_ENC_MASK, FLAG_SERIAL, FLAG_MEL_BF16 = 1, 2, 4, 8
 
 
+# Static outputs of graph replays that another stream is still reading (data.OutputFetcher's device -> host copies):
+# (device index, data_ptr of pred_melspec) -> events the next replay into that buffer must wait for.  record_stream()
+# cannot protect these tensors -- they live in a graph's private pool and the replay overwrites them regardless.
+_STATIC_OUTPUT_READERS: Dict[tuple, list] = {}
+
+
+def note_output_read(pred: torch.Tensor, event: "torch.cuda.Event") -> bool:
+    """Tell the module that `event` (recorded on the reader's stream) marks the end of a cross-stream read of the forward
+    outputs whose `pred_melspec` is `pred`.  No-op (False) unless that tensor is a static graph output."""
+    readers = _STATIC_OUTPUT_READERS.get((pred.device.index, pred.data_ptr()))
+    if readers is None:
+        return False
+    readers.append(event)
+    return True
+
+
+class _GraphEntry:
+    """One captured forward per output set, sharing static INPUT buffers the caller's tensors are copied into."""
+    __slots__ = ("inputs", "sets", "turn", "weights", "launches")
+
+
 class _Holder(nn.Module):
     """Plain container node so that parameter names reproduce the reference's dotted keys."""
 
@@ -128,6 +149,7 @@ class TransformerTTS(nn.Module):
         self.n_phon = n_phon
         self.serial_encoder = False   # True: keep the encoder branch on the caller's stream (no side stream)
         self.use_cuda_graph = False   # True: replay the forward as a CUDA graph (static output buffers; _forward_graph)
+        self.graph_output_sets = 2    # static output sets a graph entry rotates through (next call never overwrites the last result)
         self._graphs = {}
         self.graph_launches = 0       # kernel launches executed by graph replays (tts_launch_count sees only captures)
         self.strict_lens = False      # True: reproduce the reference's Tp == max(lens) assert (costs a host sync)
@@ -188,8 +210,14 @@ class TransformerTTS(nn.Module):
         if dev.type == "cuda":
             self.device = dev
         self._packed, self._ws, self._fp_tensors = None, None, None
-        self._graphs = {}
+        self._drop_graphs()
         return out
+
+    def _drop_graphs(self):
+        for e in self._graphs.values():
+            for _, o in e.sets:
+                _STATIC_OUTPUT_READERS.pop((o["pred_melspec"].device.index, o["pred_melspec"].data_ptr()), None)
+        self._graphs = {}
 
     def _workspace(self, B, Tp, Tm):
         need = _ext.load().tts_workspace_bytes(B, Tp, Tm) + 1024
@@ -211,11 +239,8 @@ class TransformerTTS(nn.Module):
             raise RuntimeError("transformertts_b200 accelerates eval-mode forward only (dropout off, BatchNorm running "
                                "statistics); call .eval() first. Training-mode forward/backward is out of scope.")
         lib = _ext.load()
-        phoneme, phoneme_lens = self._prep(phoneme, torch.int64), self._prep(phoneme_lens, torch.int64)
         # the target mel may arrive as bf16 (data.collate_fn(mel_dtype=bfloat16)): half the H2D bytes, no cast kernel
         mel_bf16 = melspec.dtype == torch.bfloat16
-        melspec = self._prep(melspec, torch.bfloat16 if mel_bf16 else torch.float32)
-        melspec_lens = self._prep(melspec_lens, torch.int64)
         if phoneme.dim() != 2 or melspec.dim() != 3 or melspec.shape[2] != N_MELS:
             raise ValueError("expected phoneme [B,Tp] and melspec [B,Tm,80]")
         B, Tp = phoneme.shape
@@ -224,12 +249,14 @@ class TransformerTTS(nn.Module):
             raise ValueError("batch sizes of phoneme / melspec / lens disagree")
         if self.strict_lens:   # model/model.py:294 asserts the mask width equals the padded length
             assert int(phoneme_lens.max()) == Tp and int(melspec_lens.max()) == Tm, "Size mismatch between memory and mask"
+        flags = (FLAG_ENC_MASK | (FLAG_WANT_ALIGN if return_alignments else 0) |
+                 (FLAG_SERIAL if self.serial_encoder else 0) | (FLAG_MEL_BF16 if mel_bf16 else 0))
         with torch.cuda.device(self.device):
-            flags = (FLAG_ENC_MASK | (FLAG_WANT_ALIGN if return_alignments else 0) |
-                     (FLAG_SERIAL if self.serial_encoder else 0) | (FLAG_MEL_BF16 if mel_bf16 else 0))
-            args = (phoneme, melspec, phoneme_lens, melspec_lens)
-            if self.use_cuda_graph:
-                return self._forward_graph(lib, args, B, Tp, Tm, flags, return_alignments)
+            if self.use_cuda_graph:                    # inputs are copied (cast / moved) straight into the graph's own buffers
+                return self._forward_graph(lib, (phoneme, melspec, phoneme_lens, melspec_lens), B, Tp, Tm, flags,
+                                           return_alignments)
+            args = (self._prep(phoneme, torch.int64), self._prep(melspec, torch.bfloat16 if mel_bf16 else torch.float32),
+                    self._prep(phoneme_lens, torch.int64), self._prep(melspec_lens, torch.int64))
             return self._forward_launch(lib, args, B, Tp, Tm, flags, return_alignments)
 
     def _forward_launch(self, lib, args, B, Tp, Tm, flags, return_alignments):
@@ -252,30 +279,67 @@ class TransformerTTS(nn.Module):
             "alignments": [align[l] for l in range(3)] if return_alignments else [],
         }
 
-    def _forward_graph(self, lib, args, B, Tp, Tm, flags, return_alignments):
-        """`use_cuda_graph = True`: the ~50 launches of one forward (both streams, programmatic-dependent-launch edges
-        included) are captured once per (shapes, flags, input buffers) and replayed -- 3-6 % less device time, most for
-        small batches.  As with every graph replay the OUTPUTS ARE STATIC BUFFERS: they are overwritten by the next
-        forward with the same key, and a consumer on another stream must be ordered before that call by the caller.
-        Inputs are read where they are (the key contains their addresses: a double-buffered feeder gives two graphs)."""
+    def _graph_entry(self, lib, B, Tp, Tm, flags, return_alignments) -> "_GraphEntry":
         w = self._weights()
         ws, ws_bytes = self._workspace(B, Tp, Tm)
-        key = (B, Tp, Tm, flags, tuple(t.data_ptr() for t in args), id(w), ws.value)
-        hit = self._graphs.get(key)
-        if hit is None:
-            if len(self._graphs) >= 8:                       # shapes / buffers keep changing: do not hoard graphs
-                self._graphs.pop(next(iter(self._graphs)))
-            self._forward_launch(lib, args, B, Tp, Tm, flags, return_alignments)    # warm-up outside the capture
-            torch.cuda.current_stream(self.device).synchronize()
+        key = (B, Tp, Tm, flags, id(w), ws.value)            # shapes and flags only: no caller addresses
+        e = self._graphs.get(key)
+        if e is not None:
+            return e
+        if len(self._graphs) >= 8:                           # shapes keep changing (unbucketed loader): do not hoard graphs
+            old = self._graphs.pop(next(iter(self._graphs)))
+            for _, o in old.sets:
+                _STATIC_OUTPUT_READERS.pop((o["pred_melspec"].device.index, o["pred_melspec"].data_ptr()), None)
+        dev = self.device
+        e = _GraphEntry()
+        e.inputs = (torch.zeros(B, Tp, dtype=torch.int64, device=dev),
+                    torch.zeros(B, Tm, N_MELS, dtype=torch.bfloat16 if flags & FLAG_MEL_BF16 else torch.float32, device=dev),
+                    torch.ones(B, dtype=torch.int64, device=dev), torch.ones(B, dtype=torch.int64, device=dev))
+        e.sets, e.turn, e.weights = [], 0, w                 # keep the weights of the capture alive
+        self._forward_launch(lib, e.inputs, B, Tp, Tm, flags, return_alignments)    # warm-up outside the capture
+        torch.cuda.current_stream(dev).synchronize()
+        for _ in range(max(1, int(self.graph_output_sets))):
             g = torch.cuda.CUDAGraph()
             n0 = lib.tts_launch_count()
             with torch.cuda.graph(g):
-                out = self._forward_launch(lib, args, B, Tp, Tm, flags, return_alignments)
-            hit = (g, out, args, w, int(lib.tts_launch_count() - n0))    # keep the inputs / weights of the capture alive
-            self._graphs[key] = hit
-        hit[0].replay()
-        self.graph_launches += hit[4]                        # kernels of this library executed through graph replays
-        out = hit[1]
+                out = self._forward_launch(lib, e.inputs, B, Tp, Tm, flags, return_alignments)
+            e.launches = int(lib.tts_launch_count() - n0)
+            e.sets.append((g, out))
+            _STATIC_OUTPUT_READERS[(dev.index, out["pred_melspec"].data_ptr())] = []
+        self._graphs[key] = e
+        return e
+
+    def graph_input_buffers(self, B, Tp, Tm, mel_dtype=torch.float32, return_alignments: bool = True):
+        """The static input tensors (phoneme, melspec, phoneme_lens, melspec_lens) of the graph for these shapes.  A
+        producer that writes its batch into them (and passes them to `forward`) saves the per-call input copies."""
+        flags = (FLAG_ENC_MASK | (FLAG_WANT_ALIGN if return_alignments else 0) |
+                 (FLAG_SERIAL if self.serial_encoder else 0) | (FLAG_MEL_BF16 if mel_dtype == torch.bfloat16 else 0))
+        with torch.cuda.device(self.device):
+            return self._graph_entry(_ext.load(), B, Tp, Tm, flags, return_alignments).inputs
+
+    def _forward_graph(self, lib, args, B, Tp, Tm, flags, return_alignments):
+        """`use_cuda_graph = True`: the ~50 launches of one forward (both streams, programmatic-dependent-launch edges
+        included) are captured once per (shapes, flags) and replayed -- 3-6 % less device time, most for small batches.
+        The graph reads its OWN input buffers: the caller's tensors (any device, pinned or not, any compatible dtype) are
+        copied into them on the current stream before every replay, so fresh tensors from a DataLoader never re-capture
+        (`graph_input_buffers` hands the buffers out to producers that want to skip the copy).  The OUTPUTS are static
+        buffers too; an entry rotates through `graph_output_sets` (2) of them, so a result stays intact during the next
+        call and is overwritten by the one after.  A reader on another stream registers its completion event with
+        `note_output_read` (data.OutputFetcher does) and the replay that reuses the set waits for it."""
+        e = self._graph_entry(lib, B, Tp, Tm, flags, return_alignments)
+        for dst, src in zip(e.inputs, args):
+            if src.data_ptr() != dst.data_ptr() or src.device != dst.device:
+                dst.copy_(src, non_blocking=True)
+        g, out = e.sets[e.turn]
+        e.turn = (e.turn + 1) % len(e.sets)
+        readers = _STATIC_OUTPUT_READERS.get((self.device.index, out["pred_melspec"].data_ptr()))
+        if readers:
+            cur = torch.cuda.current_stream(self.device)
+            for ev in readers:
+                cur.wait_event(ev)
+            readers.clear()
+        g.replay()
+        self.graph_launches += e.launches                    # kernels of this library executed through graph replays
         return {"pred_melspec": out["pred_melspec"], "post_melspec": out["post_melspec"], "pred_stop": out["pred_stop"],
                 "alignments": list(out["alignments"])}
 

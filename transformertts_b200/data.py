@@ -251,7 +251,7 @@ class OutputFetcher:
                         nbytes += out[k].numel() * 4
                         res[k] = h.view(out[k].shape)
             for t in (pred, post, stop):
-                t.record_stream(self.stream)
+                t.record_stream(self.stream)              # keeps allocator-owned outputs alive until the copy ran
             if self.with_alignments:
                 hs = []
                 for l, a in enumerate(out["alignments"]):
@@ -264,6 +264,10 @@ class OutputFetcher:
             ev = torch.cuda.Event()
             ev.record(self.stream)
         self._done[slot] = ev
+        # static graph outputs (model.use_cuda_graph) are not protected by record_stream: the replay that reuses this
+        # output set is made to wait for `ev`
+        from .api import note_output_read
+        note_output_read(pred, ev)
         self.d2h_bytes = nbytes
         return res
 
