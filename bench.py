@@ -796,6 +796,11 @@ def run_ours(args):
                      "align_store_bytes": align_bytes * world,
                      "roofline_ms": t_tensor + t_store, "frac_with_align_store": (t_tensor + t_store) / ms_step,
                      "hbm_write_only_gbs_probe": write_gbs,
+                     # whole-forward DRAM bytes per GPU from one ncu pass over a graph-free forward (profiles/r03_step_dram.txt)
+                     # against the bytes the step must move: inputs (phonemes, mel, lens) + outputs + alignments
+                     "step_dram_bytes": ncu_traffic("step_forward_cfg2"),
+                     "algorithmic_bytes": int(B * Tp * 8 + 2 * B * 8 + B * Tm * 80 * 4 + 2 * B * Tm * 80 * 4 + B * Tm * 4
+                                              + align_bytes),
                      "note": "roofline_ms = tensor term at the sustained bf16 peak + alignment store at the HBM "
                              "copy peak (the kernels are serial); the write-only probe shows what pure stores reach"}
 

@@ -21,6 +21,11 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REF_SRC = "/root/reference"
 DST = os.path.join(HERE, "_ref")
 FILES = ["model/__init__.py", "model/model.py", "model/layers.py", "model/module.py", "loss.py"]
+# The reference's training harness, staged in its own directory (oracle/_ref/harness/) so that importing it never puts the
+# staged `model` / `loss` on the path: tests/test_gpu_ref_harness.py runs this file UNCHANGED on the B200 module, with
+# `model`, `loss`, `utils.util` resolved to transformertts_b200 and pytorch_lightning / loguru / utils.plot stubbed.
+HARNESS_FILES = ["lightning_module.py"]
+HARNESS_DST = os.path.join(DST, "harness")
 
 
 def sha256(path):
@@ -40,6 +45,12 @@ def stage(src=REF_SRC, dst=DST):
         os.makedirs(os.path.dirname(d), exist_ok=True)
         shutil.copyfile(s, d)
         manifest["files"][rel] = sha256(d)
+    manifest["harness_files"] = {}
+    for rel in HARNESS_FILES:
+        s, d = os.path.join(src, rel), os.path.join(dst, "harness", rel)
+        os.makedirs(os.path.dirname(d), exist_ok=True)
+        shutil.copyfile(s, d)
+        manifest["harness_files"][rel] = sha256(d)
     with open(os.path.join(dst, "MANIFEST.json"), "w") as f:
         json.dump(manifest, f, indent=1, sort_keys=True)
     return manifest
@@ -64,6 +75,19 @@ def load(dst=DST):
     from model.model import TransformerTTS                  # noqa: E402  (the reference)
     from loss import TransformerTTSLoss                     # noqa: E402
     return TransformerTTS, TransformerTTSLoss
+
+
+def harness_path(name="lightning_module.py", dst=DST):
+    """Path of a staged harness file if it is present and matches its recorded hash, else None."""
+    mpath = os.path.join(dst, "MANIFEST.json")
+    if not os.path.exists(mpath):
+        return None
+    with open(mpath) as f:
+        digest = json.load(f).get("harness_files", {}).get(name)
+    p = os.path.join(dst, "harness", name)
+    if digest is None or not os.path.exists(p) or sha256(p) != digest:
+        return None
+    return p
 
 
 if __name__ == "__main__":

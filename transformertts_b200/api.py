@@ -161,6 +161,7 @@ class TransformerTTS(nn.Module):
         self._decode_capacity = None
         self._warned_capacity = False
         self._ws = None
+        self._scratch_bufs = {}
         self.register_load_state_dict_post_hook(lambda module, incompatible: module.refresh_weights())
 
     # ------------------------------------------------------------------ parameter tree
@@ -210,6 +211,7 @@ class TransformerTTS(nn.Module):
         if dev.type == "cuda":
             self.device = dev
         self._packed, self._ws, self._fp_tensors = None, None, None
+        self._scratch_bufs = {}
         self._drop_graphs()
         return out
 
@@ -226,6 +228,15 @@ class TransformerTTS(nn.Module):
         base = self._ws.data_ptr()
         aligned = (base + 1023) & ~1023
         return C.c_void_p(aligned), self._ws.numel() - (aligned - base)
+
+    def _scratch(self, name, numel, dtype):
+        """Grow-only per-module scratch for inference(); like the workspace it is shared by all calls on this module, which
+        are ordered on one stream.  The returned results are always fresh tensors (copies of the produced prefix)."""
+        t = self._scratch_bufs.get(name)
+        if t is None or t.numel() < numel or t.device != self.device:
+            t = torch.empty(numel, dtype=dtype, device=self.device)
+            self._scratch_bufs[name] = t
+        return t[:numel]
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
@@ -370,16 +381,18 @@ class TransformerTTS(nn.Module):
                 self._warned_capacity = True
             w = self._weights()
             ws, ws_bytes = self._workspace(B, Tp, 1)
-            cross_kv = torch.empty(3 * B * Tp * 512, dtype=torch.bfloat16, device=dev)
-            ph_len = torch.empty(B, dtype=torch.int32, device=dev)
+            # decode scratch (K/V caches, raw frame / stop buffers, counters) is kept by the module and only grows: a
+            # 128-row, 1000-frame call needs 393 MB of it, which is not re-requested from the allocator on every call
+            cross_kv = self._scratch("cross_kv", 3 * B * Tp * 512, torch.bfloat16)
+            ph_len = self._scratch("ph_len", B, torch.int32)
             # encoder WITHOUT key-padding mask (model/model.py:346-348)
             _ext.check(lib.tts_encode(C.byref(w.struct), _ext.ptr(phoneme), _ext.ptr(phoneme_lens), B, Tp, 0,
                                       _ext.ptr(cross_kv), _ext.ptr(ph_len), ws, ws_bytes, self._stream()), "tts_encode")
-            self_kv = torch.empty(3 * B * max_frames * 512, dtype=torch.bfloat16, device=dev)
-            mel = torch.empty(B, max_frames, N_MELS, dtype=torch.float32, device=dev)
-            stop = torch.empty(B, max_frames, dtype=torch.float32, device=dev)
-            stop_count = torch.empty(max_frames, dtype=torch.int32, device=dev)
-            n_frames = torch.empty(1, dtype=torch.int32, device=dev)
+            self_kv = self._scratch("self_kv", 3 * B * max_frames * 512, torch.bfloat16)
+            mel = self._scratch("mel", B * max_frames * N_MELS, torch.float32).view(B, max_frames, N_MELS)
+            stop = self._scratch("stop", B * max_frames, torch.float32).view(B, max_frames)
+            stop_count = self._scratch("stop_count", max_frames, torch.int32)
+            n_frames = self._scratch("n_frames", 1, torch.int32)
             forced = None
             if forced_melspec is not None:
                 forced = self._prep(forced_melspec, torch.float32)
@@ -391,8 +404,8 @@ class TransformerTTS(nn.Module):
                                       _ext.ptr(stop_count), _ext.ptr(n_frames), int(rows_per_cluster),
                                       int(cluster_size), _ext.ptr(forced), self._stream()), "tts_decode")
             n = int(n_frames.item())                  # the single host sync of the AR loop
-            pred = mel[:, :n].contiguous()
-            pred_stop = stop[:, :n].unsqueeze(-1).contiguous()     # (B,T,1)  model/model.py:378,393
+            pred = mel[:, :n].clone(memory_format=torch.contiguous_format)       # always a copy: `mel` is module scratch
+            pred_stop = stop[:, :n].unsqueeze(-1).clone(memory_format=torch.contiguous_format)   # (B,T,1)  model/model.py:378,393
             post = torch.empty_like(pred)
             ws, ws_bytes = self._workspace(B, 1, n)
             _ext.check(lib.tts_postnet(C.byref(w.struct), _ext.ptr(pred), B, n, _ext.ptr(post), ws, ws_bytes,
