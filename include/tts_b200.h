@@ -96,8 +96,9 @@ uint64_t tts_launch_count(void);
 size_t tts_workspace_bytes(int B, int Tp, int Tm);
 
 /* Teacher-forced forward.  phoneme i64 [B][Tp], mel f32 [B][Tm][80] (bf16 with TTS_FLAG_MEL_BF16), lens i64 [B]
- * (1 <= len <= T).  Not re-entrant per device unless TTS_FLAG_SERIAL is set: the encoder branch uses one side stream
- * and one fork/join event pair per device, so concurrent callers on one device must serialise or pass TTS_FLAG_SERIAL.
+ * (1 <= len <= T).  The encoder branch uses one side stream and one fork/join event pair per device; concurrent callers
+ * on one device (two host threads, two weight / workspace sets) are serialised by the library while they ENQUEUE
+ * (a per-device mutex from fork to join); their GPU work still overlaps.  TTS_FLAG_SERIAL avoids the side stream.
  * Outputs f32: mel_pre [B][Tm][80], mel_post [B][Tm][80], stop [B][Tm], align [3][B][4][Tm][Tp]
  * (align may be NULL unless TTS_FLAG_WANT_ALIGN). */
 int tts_forward(const TtsWeights* w, const int64_t* phoneme, const void* mel, const int64_t* ph_lens,

@@ -290,3 +290,36 @@ def test_full_size_properties_cfg5_long_utterances():
         mask = (torch.arange(400, device=A.device)[None, :] >= pl.to(A.device)[:, None])[:, None, None, :]
         assert float((A * mask).abs().max()) == 0.0
         assert float((A[:2] - S).abs().max()) <= 1e-6
+
+
+def test_two_models_two_threads_one_device():
+    """two modules with different weights driven from two host threads on their own streams share
+    the device's encoder side stream and fork / join events; every result must equal the single-threaded one."""
+    import threading
+    ms = [_model(O.make_state_dict(61 + i)) for i in range(2)]
+    xs = [[t.to(DEV) for t in O.make_inputs(3, 64, 200, seed=70 + i)] for i in range(2)]
+    want = []
+    for m, x in zip(ms, xs):
+        o = m(*x)
+        want.append({k: o[k].clone() for k in ("pred_melspec", "post_melspec", "pred_stop")})
+    torch.cuda.synchronize()
+    errors = []
+
+    def worker(i):
+        try:
+            st = torch.cuda.Stream(DEV)
+            with torch.cuda.stream(st):
+                for _ in range(40):
+                    o = ms[i](*xs[i])
+                    st.synchronize()
+                    for k in want[i]:
+                        if not torch.equal(o[k], want[i][k]):
+                            errors.append((i, k))
+                            return
+        except Exception as e:          # noqa: BLE001
+            errors.append((i, repr(e)))
+
+    th = [threading.Thread(target=worker, args=(i,)) for i in range(2)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errors, errors

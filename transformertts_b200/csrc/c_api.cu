@@ -369,7 +369,11 @@ static int check_common(const TtsWeights* w, int B, int Tp, int Tm, const void* 
 // chain's kernel: 1.13 -> 1.21 / 1.37 / 1.40 ms per cfg-2 forward -- every kernel is persistent with one CTA per SM, so
 // two chains only take SMs away from each other.
 #include <mutex>
-struct SideStream { cudaStream_t enc; cudaEvent_t fork, enc_join; bool ok; };
+// `use` is held by a tts_forward call from its fork to its join (host-side enqueue only, ~0.1 ms): the event pair and the
+// side stream are shared by every caller on the device, and cudaStreamWaitEvent binds to the event's LATEST record, so
+// two host threads (two models on one GPU) must not interleave their record / wait pairs.  The GPU work of the two
+// calls still overlaps: only the enqueueing is serialised.
+struct SideStream { cudaStream_t enc; cudaEvent_t fork, enc_join; bool ok; std::mutex use; };
 static SideStream* side_stream() {
   static SideStream table[kMaxDevices] = {};
   static std::mutex mu;
@@ -486,7 +490,9 @@ extern "C" int tts_forward(const TtsWeights* w, const int64_t* phoneme, const vo
   static const bool env_serial = getenv("TTS_SERIAL") != nullptr;
   SideStream* side = (env_serial || (flags & TTS_FLAG_SERIAL)) ? nullptr : side_stream();
   cudaStream_t se = s;                               // stream of the encoder branch
+  std::unique_lock<std::mutex> side_hold;
   if (side != nullptr) {
+    side_hold = std::unique_lock<std::mutex>(side->use);
     if (cudaEventRecord(side->fork, s) != cudaSuccess || cudaStreamWaitEvent(side->enc, side->fork, 0) != cudaSuccess)
       return fail("side stream fork failed");
     se = side->enc;
